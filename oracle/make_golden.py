@@ -1,0 +1,173 @@
+"""Generate tests/golden/*.pt from the REAL reference modules (build container only).
+
+    python -m oracle.make_golden
+
+Weights are NOT stored (82 M parameters): each fixture records the seed given to
+oracle/init_weights.py; the reference module is loaded from that state_dict with
+strict key checking, which also pins the key/shape contract of the weight packer.
+Inputs, injected RNG tensors and the reference's outputs are stored (all small).
+"""
+import os
+import sys
+
+import numpy as np
+import torch
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from oracle import ref_import as R          # noqa: E402
+from oracle import init_weights as W        # noqa: E402
+from oracle import hift_ref                 # noqa: E402
+
+OUT = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tests", "golden")
+
+
+def _save(name, obj):
+    os.makedirs(OUT, exist_ok=True)
+    path = os.path.join(OUT, name)
+    torch.save(obj, path)
+    print(f"wrote {path}  ({os.path.getsize(path) / 1024:.0f} KiB)")
+
+
+def _gen(seed):
+    g = torch.Generator()
+    g.manual_seed(seed)
+    return g
+
+
+def estimator(causal: bool):
+    est = R.build_estimator(causal).eval()
+    est.load_state_dict(W.flow_estimator_sd(causal, seed=0), strict=True)
+    g = _gen(100 + causal)
+    T = 40 if causal else 45
+    x, mu, cond = (torch.randn(2, 80, T, generator=g) for _ in range(3))
+    spks = torch.randn(2, 80, generator=g)
+    t = torch.tensor([0.1, 0.7])
+    mask = torch.ones(2, 1, T)
+    with torch.no_grad():
+        out = est(x, mask, mu, t, spks, cond)
+    _save(f"estimator_{'v2' if causal else 'v1'}.pt",
+          dict(weights_seed=0, causal=causal, x=x, mask=mask, mu=mu, t=t, spks=spks, cond=cond, out=out))
+
+
+def cfm(causal: bool):
+    est = R.build_estimator(causal).eval()
+    est.load_state_dict(W.flow_estimator_sd(causal, seed=0), strict=True)
+    m = R.build_cfm(causal, est)
+    g = _gen(200 + causal)
+    T, prompt_len = (30, 8) if causal else (61, 11)
+    mu = torch.randn(1, 80, T, generator=g)
+    spks = torch.randn(1, 80, generator=g)
+    cond = torch.zeros(1, 80, T)
+    cond[:, :, :prompt_len] = torch.randn(1, 80, prompt_len, generator=g) * 2 - 4
+    mask = torch.ones(1, 1, T)
+    d = dict(weights_seed=0, causal=causal, mu=mu, mask=mask, spks=spks, cond=cond, prompt_len=prompt_len, n_timesteps=10)
+    with torch.no_grad():
+        if causal:
+            mel, _ = m(mu.clone(), mask, 10, spks=spks, cond=cond)
+            d.update(z=m.rand_noise[:, :, :T].clone(), mel=mel, rand_noise_head=m.rand_noise[:, :, :64].clone())
+        else:
+            torch.manual_seed(4321)
+            mel, cache = m(mu.clone(), mask, 10, spks=spks, cond=cond, prompt_len=prompt_len)
+            torch.manual_seed(4321)
+            z = torch.randn_like(mu)
+            # second call re-using the cache (streaming, flow_matching.py:58-65)
+            mu2 = torch.randn(1, 80, T, generator=g)
+            torch.manual_seed(4322)
+            mel2, cache2 = m(mu2.clone(), mask, 10, spks=spks, cond=cond, prompt_len=prompt_len, flow_cache=cache)
+            torch.manual_seed(4322)
+            z2 = torch.randn_like(mu)
+            d.update(z=z, mel=mel, flow_cache=cache, mu2=mu2, z2=z2, mel2=mel2, flow_cache2=cache2)
+    _save(f"cfm_{'v2' if causal else 'v1'}.pt", d)
+
+
+def hift(v2: bool):
+    m = R.build_hift(v2).eval()
+    sd = W.hift_sd(v2, seed=1)
+    m.load_state_dict(sd, strict=True)
+    g = _gen(300 + v2)
+    T = 11 if v2 else 17
+    hop = hift_ref.arch(v2)["hop"]
+    while True:     # pick a mel whose predicted f0 covers voiced (>10 Hz) and unvoiced frames
+        mel = torch.randn(1, 80, T, generator=g) * 2 - 4
+        with torch.no_grad():
+            f0 = m.f0_predictor(mel)
+        if (f0 > 10).sum() >= 3 and (f0 < 10).sum() >= 2:
+            break
+    torch.manual_seed(77)
+    with torch.no_grad():
+        wav, s = m.inference(mel)
+    torch.manual_seed(77)
+    phase_vec, noise = hift_ref.draw_source_rng(1, T * hop)
+    cache_source = s[:, :, :hop * 2].clone() * 0.5
+    torch.manual_seed(78)
+    with torch.no_grad():
+        wav_c, s_c = m.inference(mel, cache_source=cache_source)
+        f0 = m.f0_predictor(mel)
+    torch.manual_seed(78)
+    phase_vec_c, noise_c = hift_ref.draw_source_rng(1, T * hop)
+    _save(f"hift_{'v2' if v2 else 'v1'}.pt",
+          dict(weights_seed=1, v2=v2, mel=mel, phase_vec=phase_vec, noise=noise, wav=wav, s=s, f0=f0,
+               cache_source=cache_source, phase_vec_c=phase_vec_c, noise_c=noise_c, wav_c=wav_c, s_c=s_c))
+
+
+def act1d():
+    R.setup()
+    from cosyvoice.BigVGAN.alias_free_activation.torch.act import Activation1d
+    from cosyvoice.BigVGAN.nnet.activations import SnakeBeta
+    g = _gen(400)
+    C, T = 24, 37
+    act = SnakeBeta(C, alpha_logscale=True)
+    with torch.no_grad():
+        act.alpha.copy_(torch.randn(C, generator=g) * 0.4)
+        act.beta.copy_(torch.randn(C, generator=g) * 0.4)
+    m = Activation1d(activation=act)
+    x = torch.randn(2, C, T, generator=g) * 2
+    with torch.no_grad():
+        y = m(x)
+    _save("act1d.pt", dict(x=x, alpha=act.alpha.detach().clone(), beta=act.beta.detach().clone(), y=y,
+                           up_filter=m.upsample.filter.reshape(-1).clone(),
+                           down_filter=m.downsample.lowpass.filter.reshape(-1).clone()))
+
+
+def bigvgan(topology="24k100"):
+    m = R.build_bigvgan(topology).eval()
+    sd = W.bigvgan_sd(topology, seed=2)
+    res = m.load_state_dict(sd, strict=False)
+    assert not res.unexpected_keys, res.unexpected_keys
+    allowed = ("input_embedding.", "encoder_proj.", "mel_proj.")
+    bad = [k for k in res.missing_keys if not k.startswith(allowed) and not k.endswith(".filter")]
+    assert not bad, bad
+    g = _gen(500)
+    B, T = 2, 9
+    in_ch = 100 if topology == "24k100" else 1024
+    feat = torch.randn(B, in_ch, T, generator=g)
+    spk = torch.randn(B, 512, 1, generator=g)
+    with torch.no_grad():      # bigvgan.py:406-436 driven through the module's own layers
+        x = m.conv_pre(feat)
+        x = x + m.cond_layer(spk)
+        for i in range(m.num_upsamples):
+            x = m.ups[i][0](x)
+            x = x + m.conds[i](spk)
+            xs = None
+            for j in range(m.num_kernels):
+                r = m.resblocks[i * m.num_kernels + j](x)
+                xs = r if xs is None else xs + r
+            x = xs / m.num_kernels
+        x = m.activation_post(x)
+        x = m.conv_post(x)
+        wav = torch.tanh(x).squeeze(1)
+    _save(f"bigvgan_{topology}.pt", dict(weights_seed=2, topology=topology, feat=feat, spk=spk, wav=wav))
+
+
+if __name__ == "__main__":
+    import warnings
+    warnings.filterwarnings("ignore")
+    torch.set_num_threads(8)
+    estimator(False)
+    estimator(True)
+    cfm(False)
+    cfm(True)
+    hift(False)
+    hift(True)
+    act1d()
+    bigvgan("24k100")
