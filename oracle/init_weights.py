@@ -164,7 +164,7 @@ def hift_sd(v2: bool, seed: int = 0) -> SD:
         for j, k in enumerate((3, 7, 11)):
             _resblock(g, sd, f"resblocks.{i * 3 + j}.", ch, k, std=0.02)
     ch = 512 // 2 ** len(rates)
-    _wn(g, sd, "conv_post.", (18, ch, 7), std=0.05)
+    _wn(g, sd, "conv_post.", (18, ch, 7), std=0.03)
     sd["conv_post.bias"] = _bias(g, 18, 0.1)
     # f0 predictor: 5 weight-normed convs + classifier; classifier scaled so f0 spans voiced/unvoiced
     cin = 80
@@ -211,6 +211,6 @@ def bigvgan_sd(topology: str = "24k100", seed: int = 0) -> SD:
     ch = ch0 // 2 ** len(rates)
     sd["activation_post.act.alpha"] = 0.3 * torch.randn(ch, generator=g)
     sd["activation_post.act.beta"] = 0.3 * torch.randn(ch, generator=g)
-    _wn(g, sd, "conv_post.", (1, ch, 7), std=0.1)
+    _wn(g, sd, "conv_post.", (1, ch, 7), std=0.01)
     sd["conv_post.bias"] = _bias(g, 1, 0.02)
     return sd
