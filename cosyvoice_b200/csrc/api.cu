@@ -1,0 +1,178 @@
+// extern "C" surface of libcvb200.so (declared in include/cvb200.h).  No torch types cross this boundary.
+#include <atomic>
+#include "common.cuh"
+#include "tapgemm.cuh"
+
+namespace cvb {
+
+namespace {
+thread_local std::string g_last_error;
+std::atomic<long long> g_launches{0};
+}  // namespace
+
+void set_last_error(const std::string& msg) { g_last_error = msg; }
+const char* get_last_error() { return g_last_error.c_str(); }
+void count_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
+
+using Layout = cvb200_layout;
+int launch_layernorm(const float*, int, void*, int, int, const float*, const float*, int, int, float, cudaStream_t);
+int launch_norm_mish(const void*, int, int, void*, int, int, const float*, const float*, const double*, const float*, int,
+                     const Layout&, int, float, cudaStream_t);
+int launch_time_sinusoid(const float*, int, int, float, float*, cudaStream_t);
+int launch_small_linear(const float*, int, int, const float*, const float*, int, int, int, float*, cudaStream_t);
+int launch_pack_cfg(const float*, const float*, const float*, const float*, void*, int, const Layout&, cudaStream_t);
+int launch_euler_cfg(float*, const float*, long long, float, float, cudaStream_t);
+int launch_nct_to_rows(const float*, long long, long long, int, void*, int, int, const Layout&, cudaStream_t);
+int launch_rows_to_nct(const float*, int, int, float*, long long, long long, const Layout&, cudaStream_t);
+int launch_attention(const void*, int, void*, int, int, const Layout&, int, float, cudaStream_t);
+int launch_rowdot_abs(const void*, int, int, const float*, const float*, int, float*, int, cudaStream_t);
+int launch_sine_source(const float*, const Layout&, int, float, const float*, const float*, const float*, const float*,
+                       double*, float*, long long, cudaStream_t);
+int launch_stft16(const float*, long long, void*, int, int, const Layout&, cudaStream_t);
+int launch_istft16(const float*, int, const Layout&, float*, long long, float, cudaStream_t);
+int launch_snake(const void*, int, int, void*, int, int, const float*, int, const Layout&, cudaStream_t);
+int launch_reflect_row0(void*, int, int, int, const Layout&, cudaStream_t);
+int launch_anti_alias_rows(const void*, int, int, void*, int, int, const float*, const float*, const float*, int,
+                           const Layout&, cudaStream_t);
+int launch_anti_alias_nct(const void*, void*, int, int, int, int, const float*, const float*, const float*, const float*,
+                          cudaStream_t);
+
+}  // namespace cvb
+
+using namespace cvb;
+#define ST(s) reinterpret_cast<cudaStream_t>(s)
+#define NEED(p, what)                                                                    \
+  do {                                                                                   \
+    if ((p) == nullptr) {                                                                \
+      set_last_error(std::string("invalid argument: null ") + what);                     \
+      return CVB_ERR_INVALID;                                                            \
+    }                                                                                    \
+  } while (0)
+
+extern "C" {
+
+const char* cvb200_last_error(void) { return get_last_error(); }
+int cvb200_version(void) { return 100; }
+int64_t cvb200_launch_count(void) { return (int64_t)g_launches.load(); }
+
+int cvb200_tapgemm(const cvb200_gemm* p, int engine, void* stream) {
+  NEED(p, "gemm descriptor");
+  NEED(p->A, "A"); NEED(p->W, "W"); NEED(p->tile_seq, "tile_seq"); NEED(p->tile_row0, "tile_row0"); NEED(p->seq_len, "seq_len");
+  if (p->m_tiles == 0) return CVB_OK;
+  if (engine == CVB200_ENGINE_TCGEN05) return launch_tapgemm_tc(*p, ST(stream));
+  if (engine == CVB200_ENGINE_SIMT) return launch_tapgemm_simt(*p, ST(stream));
+  set_last_error("invalid argument: unknown engine");
+  return CVB_ERR_INVALID;
+}
+
+int cvb200_layernorm(const float* x, int ldx, void* out, int ldo, int out_dt, const float* gamma, const float* beta,
+                     int rows, int C, float eps, void* stream) {
+  NEED(x, "x"); NEED(out, "out"); NEED(gamma, "gamma"); NEED(beta, "beta");
+  return launch_layernorm(x, ldx, out, ldo, out_dt, gamma, beta, rows, C, eps, ST(stream));
+}
+
+int cvb200_norm_mish(const void* h, int ldh, int h_dt, void* out, int ldo, int out_dt, const float* gamma,
+                     const float* beta, const double* gn_stats, const float* seq_bias, int seq_bias_ld,
+                     const cvb200_layout* lay, int C, float eps, void* stream) {
+  NEED(h, "h"); NEED(out, "out"); NEED(gamma, "gamma"); NEED(beta, "beta"); NEED(lay, "layout");
+  return launch_norm_mish(h, ldh, h_dt, out, ldo, out_dt, gamma, beta, gn_stats, seq_bias, seq_bias_ld, *lay, C, eps,
+                          ST(stream));
+}
+
+int cvb200_attention(const void* qkv, int ld, void* out, int ldo, int dt, const cvb200_layout* lay, int heads,
+                     float scale, void* stream) {
+  NEED(qkv, "qkv"); NEED(out, "out"); NEED(lay, "layout");
+  return launch_attention(qkv, ld, out, ldo, dt, *lay, heads, scale, ST(stream));
+}
+
+int cvb200_time_sinusoid(const float* t, int S, int dim, float scale, float* out, void* stream) {
+  NEED(t, "t"); NEED(out, "out");
+  return launch_time_sinusoid(t, S, dim, scale, out, ST(stream));
+}
+
+int cvb200_small_linear(const float* x, int S, int K, const float* W, const float* b, int N, int pre_act,
+                        int post_act, float* y, void* stream) {
+  NEED(x, "x"); NEED(W, "W"); NEED(y, "y");
+  return launch_small_linear(x, S, K, W, b, N, pre_act, post_act, y, ST(stream));
+}
+
+int cvb200_pack_cfg_input(const float* x, const float* mu, const float* cond, const float* spks, void* out,
+                          int out_dt, const cvb200_layout* lay1, void* stream) {
+  NEED(x, "x"); NEED(mu, "mu"); NEED(cond, "cond"); NEED(spks, "spks"); NEED(out, "out"); NEED(lay1, "layout");
+  return launch_pack_cfg(x, mu, cond, spks, out, out_dt, *lay1, ST(stream));
+}
+
+int cvb200_euler_cfg(float* x, const float* v, int64_t n_half, float dt, float cfg_rate, void* stream) {
+  NEED(x, "x"); NEED(v, "v");
+  return launch_euler_cfg(x, v, (long long)n_half, dt, cfg_rate, ST(stream));
+}
+
+int cvb200_rowdot_abs(const void* x, int ldx, int x_dt, const float* w, const float* b, int K, float* out, int rows,
+                      void* stream) {
+  NEED(x, "x"); NEED(w, "w"); NEED(b, "b"); NEED(out, "out");
+  return launch_rowdot_abs(x, ldx, x_dt, w, b, K, out, rows, ST(stream));
+}
+
+int cvb200_sine_source(const float* f0, const cvb200_layout* lay0, int hop, float sr, const float* noise,
+                       const float* phase, const float* lin_w, const float* lin_b, double* prefix_ws, float* s,
+                       int64_t l_max, void* stream) {
+  NEED(f0, "f0"); NEED(lay0, "layout"); NEED(noise, "noise"); NEED(phase, "phase"); NEED(lin_w, "lin_w");
+  NEED(lin_b, "lin_b"); NEED(prefix_ws, "prefix_ws"); NEED(s, "s");
+  return launch_sine_source(f0, *lay0, hop, sr, noise, phase, lin_w, lin_b, prefix_ws, s, (long long)l_max, ST(stream));
+}
+
+int cvb200_stft16(const float* s, int64_t l_max, void* out, int ldo, int out_dt, const cvb200_layout* lay,
+                  void* stream) {
+  NEED(s, "s"); NEED(out, "out"); NEED(lay, "layout");
+  return launch_stft16(s, (long long)l_max, out, ldo, out_dt, *lay, ST(stream));
+}
+
+int cvb200_istft16(const float* x, int ldx, const cvb200_layout* lay, float* wav, int64_t l_max, float audio_limit,
+                   void* stream) {
+  NEED(x, "x"); NEED(lay, "layout"); NEED(wav, "wav");
+  return launch_istft16(x, ldx, *lay, wav, (long long)l_max, audio_limit, ST(stream));
+}
+
+int cvb200_snake(const void* x, int ldx, int x_dt, void* out, int ldo, int out_dt, const float* alpha, int C,
+                 const cvb200_layout* lay, void* stream) {
+  NEED(x, "x"); NEED(out, "out"); NEED(alpha, "alpha"); NEED(lay, "layout");
+  return launch_snake(x, ldx, x_dt, out, ldo, out_dt, alpha, C, *lay, ST(stream));
+}
+
+int cvb200_reflect_row0(void* x, int ldx, int dt, int C, const cvb200_layout* lay, void* stream) {
+  NEED(x, "x"); NEED(lay, "layout");
+  return launch_reflect_row0(x, ldx, dt, C, *lay, ST(stream));
+}
+
+int cvb200_anti_alias_act_nct(const void* x, void* y, int dt, int B, int C, int T, const float* up_filter,
+                              const float* down_filter, const float* alpha, const float* beta, void* stream) {
+  if (B > 0 && C > 0 && T > 0) {
+    NEED(x, "x"); NEED(y, "y"); NEED(up_filter, "up_filter"); NEED(down_filter, "down_filter");
+    NEED(alpha, "alpha"); NEED(beta, "beta");
+  }
+  if (dt != CVB200_F32 && dt != CVB200_BF16) {
+    set_last_error("invalid argument: unsupported dtype (the reference raises AT_ERROR, type_shim.h:41-42)");
+    return CVB_ERR_INVALID;
+  }
+  return launch_anti_alias_nct(x, y, dt, B, C, T, up_filter, down_filter, alpha, beta, ST(stream));
+}
+
+int cvb200_anti_alias_act_rows(const void* x, int ldx, int x_dt, void* out, int ldo, int out_dt, const float* filt,
+                               const float* alpha, const float* beta, int C, const cvb200_layout* lay, void* stream) {
+  NEED(x, "x"); NEED(out, "out"); NEED(filt, "filt"); NEED(alpha, "alpha"); NEED(beta, "beta"); NEED(lay, "layout");
+  return launch_anti_alias_rows(x, ldx, x_dt, out, ldo, out_dt, filt, alpha, beta, C, *lay, ST(stream));
+}
+
+int cvb200_nct_to_rows(const float* src, int64_t seq_stride, int64_t c_stride, int C, void* out, int ldo, int out_dt,
+                       const cvb200_layout* lay, void* stream) {
+  NEED(src, "src"); NEED(out, "out"); NEED(lay, "layout");
+  return launch_nct_to_rows(src, (long long)seq_stride, (long long)c_stride, C, out, ldo, out_dt, *lay, ST(stream));
+}
+
+int cvb200_rows_to_nct(const float* src, int lds, int C, float* out, int64_t seq_stride, int64_t c_stride,
+                       const cvb200_layout* lay, void* stream) {
+  NEED(src, "src"); NEED(out, "out"); NEED(lay, "layout");
+  return launch_rows_to_nct(src, lds, C, out, (long long)seq_stride, (long long)c_stride, *lay, ST(stream));
+}
+
+}  // extern "C"

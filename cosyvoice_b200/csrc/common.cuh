@@ -43,7 +43,12 @@ const char* get_last_error();
     if (_s != CVB_OK) return _s; \
   } while (0)
 
-#define CVB_LAUNCH_CHECK() CVB_CUDA(cudaGetLastError())
+void count_launch();
+#define CVB_LAUNCH_CHECK()       \
+  do {                           \
+    ::cvb::count_launch();       \
+    CVB_CUDA(cudaGetLastError()); \
+  } while (0)
 
 // ---------------------------------------------------------------- dtypes
 // Activation/weight storage type of a run: fp32 (parity mode, CUDA cores) or bf16 (tensor cores).

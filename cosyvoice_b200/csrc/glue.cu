@@ -1,0 +1,342 @@
+// Memory-bound glue of the flow estimator / CFM solver: LayerNorm, GroupNorm|LayerNorm + Mish
+// (+ time bias, mask), timestep embedding, tiny fp32 linears, CFG input packing, fused CFG + Euler
+// update, and the [C,T] <-> time-major transposes.  Warp-shuffle reductions, 128-bit accesses.
+#include "common.cuh"
+#include "tapgemm.cuh"
+
+namespace cvb {
+
+using Layout = cvb200_layout;
+
+// ---------------------------------------------------------------------------- row helpers
+// 8 consecutive channels of one row, as floats.
+template <typename T> __device__ __forceinline__ void load8(const T* p, float (&v)[8]);
+template <> __device__ __forceinline__ void load8<float>(const float* p, float (&v)[8]) {
+  const float4 a = *reinterpret_cast<const float4*>(p), b = *reinterpret_cast<const float4*>(p + 4);
+  v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
+}
+template <> __device__ __forceinline__ void load8<__nv_bfloat16>(const __nv_bfloat16* p, float (&v)[8]) {
+  const uint4 u = *reinterpret_cast<const uint4*>(p);
+  const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&u);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const float2 f = __bfloat1622float2(h[i]);
+    v[2 * i] = f.x; v[2 * i + 1] = f.y;
+  }
+}
+__device__ __forceinline__ void store8(void* base, size_t idx, int dt, const float (&v)[8]) {
+  if (dt == DT_BF16) {
+    uint4 pk;
+    __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&pk);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) h[i] = __floats2bfloat162_rn(v[2 * i], v[2 * i + 1]);
+    *reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(base) + idx) = pk;
+  } else {
+    float* o = reinterpret_cast<float*>(base) + idx;
+    *reinterpret_cast<float4*>(o) = make_float4(v[0], v[1], v[2], v[3]);
+    *reinterpret_cast<float4*>(o + 4) = make_float4(v[4], v[5], v[6], v[7]);
+  }
+}
+__device__ __forceinline__ void load8_dt(const void* base, size_t idx, int dt, float (&v)[8]) {
+  if (dt == DT_BF16) load8<__nv_bfloat16>(reinterpret_cast<const __nv_bfloat16*>(base) + idx, v);
+  else load8<float>(reinterpret_cast<const float*>(base) + idx, v);
+}
+
+// ---------------------------------------------------------------------------- LayerNorm(256)
+// one warp per row; lane owns channels [8*lane, 8*lane+8)
+__global__ void __launch_bounds__(256) layernorm256_kernel(const float* __restrict__ x, int ldx, void* __restrict__ out,
+                                                           int ldo, int out_dt, const float* __restrict__ gamma,
+                                                           const float* __restrict__ beta, int rows, float eps) {
+  const int row = blockIdx.x * 8 + (threadIdx.x >> 5);
+  const int lane = threadIdx.x & 31;
+  if (row >= rows) return;
+  float v[8];
+  load8<float>(x + (size_t)row * ldx + lane * 8, v);
+  float s = 0.f;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) s += v[i];
+  const float mean = warp_sum(s) * (1.f / 256.f);
+  float q = 0.f;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) { v[i] -= mean; q += v[i] * v[i]; }
+  const float rstd = rsqrtf(warp_sum(q) * (1.f / 256.f) + eps);
+  float g[8], b[8];
+  load8<float>(gamma + lane * 8, g);
+  load8<float>(beta + lane * 8, b);
+#pragma unroll
+  for (int i = 0; i < 8; ++i) v[i] = v[i] * rstd * g[i] + b[i];
+  store8(out, (size_t)row * ldo + lane * 8, out_dt, v);
+}
+
+// ---------------------------------------------------------------------------- Norm + Mish (Block1D tail)
+__global__ void __launch_bounds__(256) norm_mish256_kernel(const void* __restrict__ h, int ldh, int h_dt,
+                                                           void* __restrict__ out, int ldo, int out_dt,
+                                                           const float* __restrict__ gamma, const float* __restrict__ beta,
+                                                           const double* __restrict__ gn_stats,
+                                                           const float* __restrict__ seq_bias, int seq_bias_ld,
+                                                           const Layout lay, float eps) {
+  const int row = blockIdx.x * 8 + (threadIdx.x >> 5);
+  const int lane = threadIdx.x & 31;
+  if (row >= lay.rows) return;
+  const int tile = row >> 7;
+  const int b = __ldg(lay.tile_seq + tile);
+  const int lrow = __ldg(lay.tile_row0 + tile) + (row & 127);
+  const int len = __ldg(lay.seq_len + b);
+  float v[8];
+  if (lrow >= len) {
+#pragma unroll
+    for (int i = 0; i < 8; ++i) v[i] = 0.f;
+    store8(out, (size_t)row * ldo + lane * 8, out_dt, v);
+    return;
+  }
+  load8_dt(h, (size_t)row * ldh + lane * 8, h_dt, v);
+  float mean, rstd;
+  if (gn_stats) {
+    // GroupNorm(8, 256): group = 32 channels = 4 lanes; statistics over 32 channels x len frames
+    const int g = lane >> 2;
+    const double n = (double)len * 32.0;
+    const double s = gn_stats[((size_t)b * 8 + g) * 2], q = gn_stats[((size_t)b * 8 + g) * 2 + 1];
+    const double m = s / n;
+    double var = q / n - m * m;
+    if (var < 0.0) var = 0.0;
+    mean = (float)m;
+    rstd = (float)(1.0 / sqrt(var + (double)eps));
+#pragma unroll
+    for (int i = 0; i < 8; ++i) v[i] -= mean;
+  } else {
+    float s = 0.f;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) s += v[i];
+    mean = warp_sum(s) * (1.f / 256.f);
+    float q = 0.f;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) { v[i] -= mean; q += v[i] * v[i]; }
+    rstd = rsqrtf(warp_sum(q) * (1.f / 256.f) + eps);
+  }
+  float g8[8], b8[8];
+  load8<float>(gamma + lane * 8, g8);
+  load8<float>(beta + lane * 8, b8);
+#pragma unroll
+  for (int i = 0; i < 8; ++i) v[i] = mishf(v[i] * rstd * g8[i] + b8[i]);
+  if (seq_bias) {
+    float t8[8];
+    load8<float>(seq_bias + (size_t)b * seq_bias_ld + lane * 8, t8);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) v[i] += t8[i];
+  }
+  store8(out, (size_t)row * ldo + lane * 8, out_dt, v);
+}
+
+// ---------------------------------------------------------------------------- time embedding
+__global__ void time_sinusoid_kernel(const float* __restrict__ t, int S, int dim, float scale, float* __restrict__ out) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  const int half = dim / 2;
+  if (i >= S * half) return;
+  const int s = i / half, j = i - s * half;
+  const float k = logf(10000.f) / (float)(half - 1);
+  const float e = scale * t[s] * expf((float)j * -k);
+  out[(size_t)s * dim + j] = sinf(e);
+  out[(size_t)s * dim + half + j] = cosf(e);
+}
+
+__device__ __forceinline__ float small_act(int act, float v) {
+  switch (act) {
+    case ACT_MISH: return mishf(v);
+    case ACT_SILU: return v / (1.f + expf(-v));
+    case ACT_GELU: return gelu_erf(v);
+    case ACT_TANH: return tanhf(v);
+    default: return v;
+  }
+}
+
+// one warp per output column n; loops over the S rows.  K % 32 == 0, K <= 1024.
+__global__ void __launch_bounds__(256) small_linear_kernel(const float* __restrict__ x, int S, int K,
+                                                           const float* __restrict__ W, const float* __restrict__ b,
+                                                           int N, int pre_act, int post_act, float* __restrict__ y) {
+  const int n = blockIdx.x * 8 + (threadIdx.x >> 5);
+  const int lane = threadIdx.x & 31;
+  if (n >= N) return;
+  float w[32];
+  const int per = K / 32;
+#pragma unroll
+  for (int i = 0; i < 32; ++i) w[i] = i < per ? __ldg(W + (size_t)n * K + i * 32 + lane) : 0.f;
+  const float bias = b ? __ldg(b + n) : 0.f;
+  for (int s = 0; s < S; ++s) {
+    float acc = 0.f;
+#pragma unroll
+    for (int i = 0; i < 32; ++i)
+      if (i < per) acc = fmaf(small_act(pre_act, __ldg(x + (size_t)s * K + i * 32 + lane)), w[i], acc);
+    acc = warp_sum(acc);
+    if (lane == 0) y[(size_t)s * N + n] = small_act(post_act, acc + bias);
+  }
+}
+
+// ---------------------------------------------------------------------------- CFG input packing
+// out row r of the 2B-sequence layout: r < rows1 -> [x | mu | spks[b] | cond], else [x | 0 | 0 | 0]
+__global__ void __launch_bounds__(256) pack_cfg_kernel(const float* __restrict__ x, const float* __restrict__ mu,
+                                                       const float* __restrict__ cond, const float* __restrict__ spks,
+                                                       void* __restrict__ out, int out_dt, const Layout lay) {
+  // one thread per (row of the pair layout, 8-channel chunk): 320 / 8 = 40 chunks per row
+  const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const long long total = 2LL * lay.rows * 40;
+  if (idx >= total) return;
+  const int chunk = (int)(idx % 40);
+  const long long r2 = idx / 40;
+  const bool uncond = r2 >= lay.rows;
+  const int r = (int)(uncond ? r2 - lay.rows : r2);
+  const int tile = r >> 7;
+  const int b = __ldg(lay.tile_seq + tile);
+  const int lrow = __ldg(lay.tile_row0 + tile) + (r & 127);
+  const bool valid = lrow < __ldg(lay.seq_len + b);
+  float v[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) v[i] = 0.f;
+  if (valid) {
+    const int sect = chunk / 10, c0 = (chunk % 10) * 8;
+    if (sect == 0) load8<float>(x + (size_t)r * 80 + c0, v);
+    else if (!uncond) {
+      if (sect == 1) load8<float>(mu + (size_t)r * 80 + c0, v);
+      else if (sect == 2) load8<float>(spks + (size_t)b * 80 + c0, v);
+      else load8<float>(cond + (size_t)r * 80 + c0, v);
+    }
+  }
+  store8(out, (size_t)r2 * 320 + chunk * 8, out_dt, v);
+}
+
+__global__ void __launch_bounds__(256) euler_cfg_kernel(float* __restrict__ x, const float* __restrict__ v, long long n4,
+                                                        float dt, float cfg) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n4) return;
+  float4 xv = reinterpret_cast<float4*>(x)[i];
+  const float4 vc = reinterpret_cast<const float4*>(v)[i];
+  const float4 vu = reinterpret_cast<const float4*>(v)[n4 + i];
+  const float a = 1.f + cfg;
+  xv.x += dt * (a * vc.x - cfg * vu.x);
+  xv.y += dt * (a * vc.y - cfg * vu.y);
+  xv.z += dt * (a * vc.z - cfg * vu.z);
+  xv.w += dt * (a * vc.w - cfg * vu.w);
+  reinterpret_cast<float4*>(x)[i] = xv;
+}
+
+// ---------------------------------------------------------------------------- layout transposes
+// [B, C, T] (fp32) -> time-major rows.  32x32 smem tile transpose; grid (row tiles of 32, C tiles of 32).
+__global__ void __launch_bounds__(256) nct_to_rows_kernel(const float* __restrict__ src, long long seq_stride,
+                                                          long long c_stride, int C, void* __restrict__ out, int ldo,
+                                                          int out_dt, const Layout lay) {
+  __shared__ float tile[32][33];
+  const int r0 = blockIdx.x * 32, c0 = blockIdx.y * 32;
+  const int t128 = r0 >> 7;
+  const int b = __ldg(lay.tile_seq + t128);
+  const int l0 = __ldg(lay.tile_row0 + t128) + (r0 & 127);
+  const int len = __ldg(lay.seq_len + b);
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  for (int j = ty; j < 32; j += 8) {      // j: channel within tile, tx: time within tile (coalesced along T)
+    const int c = c0 + j, l = l0 + tx;
+    tile[j][tx] = (c < C && l < len) ? src[(size_t)b * seq_stride + (size_t)c * c_stride + l] : 0.f;
+  }
+  __syncthreads();
+  for (int j = ty; j < 32; j += 8) {      // j: time, tx: channel (coalesced along C)
+    const int c = c0 + tx;
+    if (c < C) st_from_float(out, (size_t)(r0 + j) * ldo + c, out_dt, tile[tx][j]);
+  }
+}
+
+__global__ void __launch_bounds__(256) rows_to_nct_kernel(const float* __restrict__ src, int lds, int C,
+                                                          float* __restrict__ out, long long seq_stride,
+                                                          long long c_stride, const Layout lay) {
+  __shared__ float tile[32][33];
+  const int r0 = blockIdx.x * 32, c0 = blockIdx.y * 32;
+  const int t128 = r0 >> 7;
+  const int b = __ldg(lay.tile_seq + t128);
+  const int l0 = __ldg(lay.tile_row0 + t128) + (r0 & 127);
+  const int len = __ldg(lay.seq_len + b);
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  for (int j = ty; j < 32; j += 8) {      // j: time, tx: channel
+    const int c = c0 + tx;
+    tile[j][tx] = c < C ? src[(size_t)(r0 + j) * lds + c] : 0.f;
+  }
+  __syncthreads();
+  for (int j = ty; j < 32; j += 8) {      // j: channel, tx: time
+    const int c = c0 + j, l = l0 + tx;
+    if (c < C && l < len) out[(size_t)b * seq_stride + (size_t)c * c_stride + l] = tile[tx][j];
+  }
+}
+
+// ---------------------------------------------------------------------------- launchers
+int launch_layernorm(const float* x, int ldx, void* out, int ldo, int out_dt, const float* gamma, const float* beta,
+                     int rows, int C, float eps, cudaStream_t st) {
+  CVB_REQUIRE(C == 256, "LayerNorm kernel is specialised for 256 channels");
+  CVB_REQUIRE(ldx % 4 == 0 && ldo % 8 == 0, "leading dimensions must keep 16-byte alignment");
+  if (rows <= 0) return CVB_OK;
+  layernorm256_kernel<<<ceil_div(rows, 8), 256, 0, st>>>(x, ldx, out, ldo, out_dt, gamma, beta, rows, eps);
+  CVB_LAUNCH_CHECK();
+  return CVB_OK;
+}
+
+int launch_norm_mish(const void* h, int ldh, int h_dt, void* out, int ldo, int out_dt, const float* gamma,
+                     const float* beta, const double* gn_stats, const float* seq_bias, int seq_bias_ld,
+                     const Layout& lay, int C, float eps, cudaStream_t st) {
+  CVB_REQUIRE(C == 256, "Norm+Mish kernel is specialised for 256 channels");
+  CVB_REQUIRE(ldh % 8 == 0 && ldo % 8 == 0, "leading dimensions must keep 16-byte alignment");
+  if (lay.rows <= 0) return CVB_OK;
+  norm_mish256_kernel<<<ceil_div(lay.rows, 8), 256, 0, st>>>(h, ldh, h_dt, out, ldo, out_dt, gamma, beta, gn_stats,
+                                                             seq_bias, seq_bias_ld, lay, eps);
+  CVB_LAUNCH_CHECK();
+  return CVB_OK;
+}
+
+int launch_time_sinusoid(const float* t, int S, int dim, float scale, float* out, cudaStream_t st) {
+  CVB_REQUIRE(dim % 2 == 0 && dim >= 4, "dim must be even");
+  if (S <= 0) return CVB_OK;
+  const int n = S * dim / 2;
+  time_sinusoid_kernel<<<ceil_div(n, 128), 128, 0, st>>>(t, S, dim, scale, out);
+  CVB_LAUNCH_CHECK();
+  return CVB_OK;
+}
+
+int launch_small_linear(const float* x, int S, int K, const float* W, const float* b, int N, int pre_act, int post_act,
+                        float* y, cudaStream_t st) {
+  CVB_REQUIRE(K % 32 == 0 && K <= 1024, "K must be a multiple of 32 and <= 1024");
+  if (S <= 0 || N <= 0) return CVB_OK;
+  small_linear_kernel<<<ceil_div(N, 8), 256, 0, st>>>(x, S, K, W, b, N, pre_act, post_act, y);
+  CVB_LAUNCH_CHECK();
+  return CVB_OK;
+}
+
+int launch_pack_cfg(const float* x, const float* mu, const float* cond, const float* spks, void* out, int out_dt,
+                    const Layout& lay, cudaStream_t st) {
+  const long long total = 2LL * lay.rows * 40;
+  if (total <= 0) return CVB_OK;
+  pack_cfg_kernel<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(x, mu, cond, spks, out, out_dt, lay);
+  CVB_LAUNCH_CHECK();
+  return CVB_OK;
+}
+
+int launch_euler_cfg(float* x, const float* v, long long n_half, float dt, float cfg, cudaStream_t st) {
+  CVB_REQUIRE(n_half % 4 == 0, "element count must be a multiple of 4");
+  const long long n4 = n_half / 4;
+  if (n4 <= 0) return CVB_OK;
+  euler_cfg_kernel<<<(unsigned)((n4 + 255) / 256), 256, 0, st>>>(x, v, n4, dt, cfg);
+  CVB_LAUNCH_CHECK();
+  return CVB_OK;
+}
+
+int launch_nct_to_rows(const float* src, long long seq_stride, long long c_stride, int C, void* out, int ldo, int out_dt,
+                       const Layout& lay, cudaStream_t st) {
+  if (lay.rows <= 0) return CVB_OK;
+  dim3 grid(lay.rows / 32, ceil_div(C, 32));
+  nct_to_rows_kernel<<<grid, 256, 0, st>>>(src, seq_stride, c_stride, C, out, ldo, out_dt, lay);
+  CVB_LAUNCH_CHECK();
+  return CVB_OK;
+}
+
+int launch_rows_to_nct(const float* src, int lds, int C, float* out, long long seq_stride, long long c_stride,
+                       const Layout& lay, cudaStream_t st) {
+  if (lay.rows <= 0) return CVB_OK;
+  dim3 grid(lay.rows / 32, ceil_div(C, 32));
+  rows_to_nct_kernel<<<grid, 256, 0, st>>>(src, lds, C, out, seq_stride, c_stride, lay);
+  CVB_LAUNCH_CHECK();
+  return CVB_OK;
+}
+
+}  // namespace cvb

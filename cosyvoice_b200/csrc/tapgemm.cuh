@@ -14,69 +14,19 @@
 // the sequence's valid length are written as zeros (they are the conv zero padding of the next op).
 #pragma once
 #include "common.cuh"
+#include "../../include/cvb200.h"
 
 namespace cvb {
 
-constexpr int MAX_SEGS = 32;   // n_phase * n_seg <= MAX_SEGS
-constexpr int GEMM_BK = 64;    // K chunk (elements); seg_len must be a multiple
+constexpr int MAX_SEGS = CVB200_MAX_SEGS;   // n_phase * n_seg <= MAX_SEGS
+constexpr int GEMM_BK = 64;    // K chunk (elements) of the tcgen05 engine; seg_len must be a multiple
 
-enum Act : int { ACT_NONE = 0, ACT_GELU = 1, ACT_ELU = 2, ACT_SNAKE = 3, ACT_LRELU = 4, ACT_MISH = 5, ACT_TANH = 6 };
+enum Act : int { ACT_NONE = 0, ACT_GELU = 1, ACT_ELU = 2, ACT_SNAKE = 3, ACT_LRELU = 4, ACT_MISH = 5, ACT_TANH = 6, ACT_SILU = 7 };
 enum ResKind : int { RES_NONE = 0, RES_F32 = 1, RES_ACT = 2 };
 enum Out1Mode : int { OUT1_NONE = 0, OUT1_COPY = 1, OUT1_SNAKE = 2, OUT1_LRELU = 3 };
 
-struct Epi {
-  // v = acc + bias[n] + seq_bias[b][n];  v = act(v);  v += res[m][col];  v *= out_scale;
-  // if (accumulate) v += out0[m][col];  rows beyond the valid length -> 0;
-  // out0[m][col] = v;  out1[m][col] = out1_fn(v);  gn_stats[b][n/32] += (v, v^2)
-  const float* bias;        // [n_phase? no: N] shared by all phases, nullable
-  const float* seq_bias;    // [n_seq][seq_bias_ld], nullable (time-embedding / speaker conditioning)
-  int seq_bias_ld;
-  int act;                  // Act
-  const float* act_alpha;   // ACT_SNAKE: per-channel alpha [N]
-  float act_slope;          // ACT_LRELU
-  int res_kind;             // ResKind
-  const void* res;          // [rows, ldr] (+ same column mapping as out0)
-  int ldr;
-  int res_dt;               // DType when RES_ACT
-  float out_scale;
-  int accumulate;
-  void* out0;
-  int ldo0;
-  int out0_dt;              // DType
-  int phase_col;            // column stride between phases in out0/out1/res (ConvTranspose: Cout stride)
-  int out1_mode;            // Out1Mode
-  void* out1;
-  int ldo1;
-  int out1_dt;
-  const float* out1_alpha;  // OUT1_SNAKE alpha [N]
-  float out1_slope;
-  double* gn_stats;         // [n_seq][N/32][2] (sum, sumsq) accumulated with atomics, nullable
-  int gn_groups;            // N/32
-  int vt_mode;              // 1: columns >= vt_col0 are stored transposed for attention: see attention.cuh
-  int vt_col0;
-  void* vt_out;             // [n_seq*heads][64][vt_ld]  (V^T, keys contiguous)
-  int vt_ld;
-};
-
-struct GemmParams {
-  const void* A;            // activation view [a_rows, lda], dtype dt
-  int lda;                  // elements
-  int a_rows;               // rows of the view (bounds for zero fill)
-  int a_cols;               // valid columns of the view (columns >= a_cols read as zero)
-  const void* W;            // packed weights [n_phase][n_pad][K], K = n_seg*seg_len, dtype dt
-  int n_pad;                // rows per phase in W (>= N)
-  int N;                    // logical output columns per phase
-  int n_phase, n_seg, seg_len;
-  short seg_row[MAX_SEGS];  // [phase*n_seg + seg]
-  short seg_col[MAX_SEGS];
-  int dt;                   // DType of A and W
-  int m_tiles;              // number of 128-row tiles
-  const int* tile_seq;      // [m_tiles] sequence index of the tile
-  const int* tile_row0;     // [m_tiles] local (within-sequence) row of the tile's first row
-  const int* seq_len;       // [n_seq] valid M-space rows
-  const int* out_limit;     // [n_seq] valid logical output rows: (lrow*n_phase + phase) < out_limit, nullable -> seq_len*n_phase
-  Epi epi;
-};
+using Epi = cvb200_epilogue;       // include/cvb200.h
+using GemmParams = cvb200_gemm;
 
 int launch_tapgemm_simt(const GemmParams& p, cudaStream_t stream);
 int launch_tapgemm_tc(const GemmParams& p, cudaStream_t stream);   // dt must be DT_BF16
@@ -90,6 +40,7 @@ __device__ __forceinline__ float apply_act(int act, float v, float alpha, float 
     case ACT_LRELU: return v > 0.f ? v : v * slope;
     case ACT_MISH: return mishf(v);
     case ACT_TANH: return tanhf(v);
+    case ACT_SILU: return siluf(v);
     default: return v;
   }
 }
@@ -133,20 +84,6 @@ __device__ __forceinline__ void epi_apply(const Epi& e, int m, int b, bool valid
   }
   // ---- stores (vectorised when the full NV chunk is in range and aligned)
   const bool full = (n0 + NV <= N);
-  if (e.vt_mode && n0 >= e.vt_col0) {
-    // transposed store of V for the attention kernel: vt_out[(b*8 + head)][d][lrow]; the caller passes
-    // m as the *global* row, and rows of one sequence are contiguous, so we use m directly:
-    // layout [heads_total][64][vt_ld] with the key index = global row m (see attention.cuh).
-#pragma unroll
-    for (int j = 0; j < NV; ++j) {
-      const int n = n0 + j;
-      if (n < N) {
-        const int hd = n - e.vt_col0;         // head*64 + d
-        st_from_float(e.vt_out, (size_t)hd * e.vt_ld + m, e.out0_dt, v[j]);
-      }
-    }
-    return;
-  }
   if (e.out0) {
     if (e.out0_dt == DT_BF16) {
       __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(e.out0) + (size_t)m * e.ldo0 + col0;

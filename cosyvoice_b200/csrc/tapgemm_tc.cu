@@ -1,0 +1,268 @@
+// tcgen05 engine of the tap GEMM (bf16 operands, fp32 accumulation in TMEM).
+//
+// Persistent, warp-specialised, one CTA per SM:
+//   warp 0   : TMA producer. One 128x64 A box per (tap segment, 64-column chunk) at row coordinate
+//              m0 + seg_row (the conv tap shift; rows outside the view are zero-filled by TMA = the
+//              conv padding) and one bn x 64 box of the packed weights, into a 4-stage smem ring.
+//   warp 1   : TMEM allocator + single-thread tcgen05.mma issuer (UMMA 128 x bn x 16, SS operands,
+//              128B-swizzled K-major descriptors), double-buffered accumulators (2 x 256 columns).
+//   warps 2-5: epilogue. tcgen05.ld the accumulator rows, fused bias / time-bias / activation /
+//              residual / scale / accumulate / dual store / GroupNorm statistics (tapgemm.cuh).
+// The epilogue of tile i overlaps the MMAs of tile i+1 through the two TMEM buffers.
+#include <cuda.h>
+#include <mutex>
+#include "ptx.cuh"
+#include "tapgemm.cuh"
+
+namespace cvb {
+
+namespace {
+
+constexpr int STAGES = 4;
+constexpr int A_STAGE_BYTES = TILE_M * GEMM_BK * 2;        // 16 KiB
+constexpr int B_STAGE_BYTES = 256 * GEMM_BK * 2;           // 32 KiB (bn <= 256)
+constexpr int BAR_BYTES = 256;
+constexpr int SMEM_BYTES = 1024 + STAGES * (A_STAGE_BYTES + B_STAGE_BYTES) + BAR_BYTES;
+constexpr int NUM_THREADS = 192;
+constexpr int TMEM_COLS = 512;
+
+template <int NV>
+__device__ __forceinline__ void epilogue_chunks(const GemmParams& p, uint32_t taddr, int bn, int n_base, int m, int b,
+                                                bool valid, int phase, float (&gs)[8], float (&gq)[8]) {
+  for (int c = 0; c < bn; c += NV) {
+    float v[NV];
+    if constexpr (NV == 32) ptx::tmem_ld32(taddr + c, v);
+    else ptx::tmem_ld16(taddr + c, v);
+    float s = 0.f, q = 0.f;
+    epi_apply<NV>(p.epi, m, b, valid, phase, n_base + c, p.N, v, false, s, q);
+    if (p.epi.gn_stats) {
+      // bn == 256 in this case (host check): chunk c covers group (n_base + c) / 32
+      const int g = ((n_base + c) >> 5) & 7;
+      gs[g] += s;
+      gq[g] += q;
+    }
+  }
+}
+
+__global__ void __launch_bounds__(NUM_THREADS, 1)
+tapgemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW,
+                  const __grid_constant__ GemmParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sA = smem;
+  uint8_t* sB = smem + STAGES * A_STAGE_BYTES;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sB + STAGES * B_STAGE_BYTES);
+  uint64_t* full = bars;                 // [STAGES]
+  uint64_t* empty = bars + STAGES;       // [STAGES]
+  uint64_t* tfull = bars + 2 * STAGES;   // [2]
+  uint64_t* tempty = tfull + 2;          // [2]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int bn = p.bn;
+  const int n_tiles = p.n_pad / bn;
+  const int total = p.m_tiles * p.n_phase * n_tiles;
+  const int chunks_per_seg = p.seg_len / GEMM_BK;
+
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < STAGES; ++i) {
+      ptx::mbar_init(&full[i], 1);
+      ptx::mbar_init(&empty[i], 1);
+    }
+    for (int i = 0; i < 2; ++i) {
+      ptx::mbar_init(&tfull[i], 1);
+      ptx::mbar_init(&tempty[i], 128);
+    }
+    ptx::fence_barrier_init();
+    ptx::prefetch_tensormap(&tmA);
+    ptx::prefetch_tensormap(&tmW);
+  }
+  if (warp == 1) ptx::tmem_alloc(tmem_slot, TMEM_COLS);
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ------------------------------------------------------------------ TMA producer
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t ph = 0;
+      for (int item = blockIdx.x; item < total; item += gridDim.x) {
+        const int nt = item % n_tiles;
+        const int rest = item / n_tiles;
+        const int phase = rest % p.n_phase;
+        const int mt = rest / p.n_phase;
+        const int m0 = mt * TILE_M;
+        const int wrow = phase * p.n_pad + nt * bn;
+        const uint32_t tx_bytes = A_STAGE_BYTES + bn * GEMM_BK * 2;
+        for (int seg = 0; seg < p.n_seg; ++seg) {
+          const int srow = p.seg_row[phase * p.n_seg + seg], scol = p.seg_col[phase * p.n_seg + seg];
+          for (int c = 0; c < chunks_per_seg; ++c) {
+            ptx::mbar_wait(&empty[stage], ph ^ 1);
+            ptx::mbar_arrive_expect_tx(&full[stage], tx_bytes);
+            ptx::tma_load_2d(sA + stage * A_STAGE_BYTES, &tmA, &full[stage], scol + c * GEMM_BK, m0 + srow);
+            ptx::tma_load_2d(sB + stage * B_STAGE_BYTES, &tmW, &full[stage], seg * p.seg_len + c * GEMM_BK, wrow);
+            if (++stage == STAGES) { stage = 0; ph ^= 1; }
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ------------------------------------------------------------------ MMA issuer
+    if (lane == 0) {
+      const uint32_t idesc = ptx::make_idesc_bf16(TILE_M, bn);
+      const int kblocks = p.n_seg * chunks_per_seg;
+      int stage = 0;
+      uint32_t ph = 0;
+      int acc = 0;
+      uint32_t acc_ph = 0;
+      for (int item = blockIdx.x; item < total; item += gridDim.x) {
+        ptx::mbar_wait(&tempty[acc], acc_ph ^ 1);
+        ptx::tc_fence_after();
+        const uint32_t d_tmem = tmem_base + acc * 256;
+        for (int kb = 0; kb < kblocks; ++kb) {
+          ptx::mbar_wait(&full[stage], ph);
+          ptx::tc_fence_after();
+          const uint32_t a_base = ptx::smem_u32(sA + stage * A_STAGE_BYTES);
+          const uint32_t b_base = ptx::smem_u32(sB + stage * B_STAGE_BYTES);
+#pragma unroll
+          for (int k = 0; k < GEMM_BK / 16; ++k) {
+            ptx::umma_ss(d_tmem, ptx::make_sw128_kmajor_desc(a_base + k * 32), ptx::make_sw128_kmajor_desc(b_base + k * 32),
+                         idesc, (kb | k) != 0);
+          }
+          ptx::umma_commit(&empty[stage]);      // frees the smem slot when these MMAs retire
+          if (++stage == STAGES) { stage = 0; ph ^= 1; }
+        }
+        ptx::umma_commit(&tfull[acc]);          // accumulator complete -> epilogue
+        acc ^= 1;
+        if (acc == 0) acc_ph ^= 1;
+      }
+    }
+  } else {
+    // ------------------------------------------------------------------ epilogue (warps 2..5)
+    const int lane_grp = warp & 3;               // TMEM lanes [32*lane_grp, +32) are accessible to this warp
+    const int row = lane_grp * 32 + lane;
+    int acc = 0;
+    uint32_t acc_ph = 0;
+    for (int item = blockIdx.x; item < total; item += gridDim.x) {
+      const int nt = item % n_tiles;
+      const int rest = item / n_tiles;
+      const int phase = rest % p.n_phase;
+      const int mt = rest / p.n_phase;
+      const int b = __ldg(p.tile_seq + mt);
+      const int lrow = __ldg(p.tile_row0 + mt) + row;
+      const int slen = __ldg(p.seq_len + b);
+      const int olim = p.out_limit ? __ldg(p.out_limit + b) : slen * p.n_phase;
+      const bool valid = lrow < slen && (lrow * p.n_phase + phase) < olim;
+      const int m = mt * TILE_M + row;
+
+      ptx::mbar_wait(&tfull[acc], acc_ph);
+      ptx::tc_fence_after();
+      const uint32_t taddr = tmem_base + ((uint32_t)(lane_grp * 32) << 16) + acc * 256;
+      float gs[8], gq[8];
+#pragma unroll
+      for (int i = 0; i < 8; ++i) gs[i] = gq[i] = 0.f;
+      if ((bn & 31) == 0) epilogue_chunks<32>(p, taddr, bn, nt * bn, m, b, valid, phase, gs, gq);
+      else epilogue_chunks<16>(p, taddr, bn, nt * bn, m, b, valid, phase, gs, gq);
+      ptx::tc_fence_before();
+      ptx::mbar_arrive(&tempty[acc]);
+      if (p.epi.gn_stats) {
+#pragma unroll
+        for (int g = 0; g < 8; ++g) {
+          const float s = warp_sum(gs[g]), q = warp_sum(gq[g]);
+          if (lane == 0 && g < p.epi.gn_groups) {
+            double* dst = p.epi.gn_stats + ((size_t)b * p.epi.gn_groups + g) * 2;
+            atomicAdd(dst, (double)s);
+            atomicAdd(dst + 1, (double)q);
+          }
+        }
+      }
+      acc ^= 1;
+      if (acc == 0) acc_ph ^= 1;
+    }
+  }
+
+  ptx::tc_fence_before();
+  __syncthreads();
+  if (warp == 1) ptx::tmem_dealloc(tmem_base, TMEM_COLS);
+}
+
+// ------------------------------------------------------------------------------------ host side
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn get_encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* ptr = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &ptr, cudaEnableDefault, &qres) == cudaSuccess &&
+        qres == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(ptr);
+  });
+  return fn;
+}
+
+int make_map_2d(CUtensorMap* map, const void* base, uint64_t cols, uint64_t rows, uint64_t row_stride_elems,
+                uint32_t box_cols, uint32_t box_rows) {
+  EncodeTiledFn fn = get_encode_fn();
+  CVB_REQUIRE(fn != nullptr, "cuTensorMapEncodeTiled not available from the driver");
+  CVB_REQUIRE((reinterpret_cast<uintptr_t>(base) & 15) == 0, "TMA base must be 16-byte aligned");
+  CVB_REQUIRE((row_stride_elems * 2) % 16 == 0, "TMA row stride must be a multiple of 16 bytes");
+  cuuint64_t dims[2] = {cols, rows};
+  cuuint64_t strides[1] = {row_stride_elems * 2};
+  cuuint32_t box[2] = {box_cols, box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    set_last_error("cuTensorMapEncodeTiled failed with CUresult " + std::to_string((int)r) + " (cols " +
+                   std::to_string(cols) + ", rows " + std::to_string(rows) + ", stride " +
+                   std::to_string(row_stride_elems) + ", box " + std::to_string(box_cols) + "x" +
+                   std::to_string(box_rows) + ")");
+    return CVB_ERR_CUDA;
+  }
+  return CVB_OK;
+}
+
+int num_sms() {
+  static int n = 0;
+  if (n == 0) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = NUM_SMS;
+  }
+  return n;
+}
+
+}  // namespace
+
+int launch_tapgemm_tc(const GemmParams& p, cudaStream_t stream) {
+  CVB_REQUIRE(p.dt == DT_BF16, "tcgen05 engine needs bf16 operands");
+  CVB_REQUIRE(p.seg_len % GEMM_BK == 0, "seg_len must be a multiple of 64");
+  CVB_REQUIRE(p.n_phase * p.n_seg <= MAX_SEGS, "too many segments");
+  CVB_REQUIRE(p.m_tiles > 0, "empty problem");
+  CVB_REQUIRE(p.bn >= 16 && p.bn <= 256 && p.bn % 16 == 0 && p.n_pad % p.bn == 0, "bad N tile");
+  CVB_REQUIRE(!p.epi.gn_stats || (p.bn == 256 && p.N == 256), "GroupNorm statistics need N == bn == 256");
+  static std::once_flag attr_once;
+  static cudaError_t attr_err = cudaSuccess;
+  std::call_once(attr_once, [] {
+    attr_err = cudaFuncSetAttribute(tapgemm_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
+  });
+  CVB_CUDA(attr_err);
+  CUtensorMap tmA, tmW;
+  CVB_TRY(make_map_2d(&tmA, p.A, (uint64_t)p.a_cols, (uint64_t)p.a_rows, (uint64_t)p.lda, GEMM_BK, TILE_M));
+  const uint64_t K = (uint64_t)p.n_seg * p.seg_len;
+  CVB_TRY(make_map_2d(&tmW, p.W, K, (uint64_t)p.n_phase * p.n_pad, K, GEMM_BK, (uint32_t)p.bn));
+  const int total = p.m_tiles * p.n_phase * (p.n_pad / p.bn);
+  const int grid = total < num_sms() ? total : num_sms();
+  tapgemm_tc_kernel<<<grid, NUM_THREADS, SMEM_BYTES, stream>>>(tmA, tmW, p);
+  CVB_LAUNCH_CHECK();
+  return CVB_OK;
+}
+
+}  // namespace cvb

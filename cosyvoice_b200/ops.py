@@ -1,0 +1,233 @@
+"""Thin Python wrappers over the C ABI (include/cvb200.h): they only marshal torch device
+pointers, shapes and the current CUDA stream.  No arithmetic happens here.
+
+`gemm_op` / the other `*_op` builders return zero-argument callables with every argument
+pre-marshalled, so that a model forward is a flat list of launches (cheap to replay and to
+capture in a CUDA graph).
+"""
+import ctypes as C
+from typing import Callable, Optional
+
+import torch
+
+from . import _lib
+from ._lib import BF16, F32
+from .layout import SeqLayout
+from .packing import TapPlan
+
+Op = Callable[[], None]
+
+
+def dt_of(t: torch.Tensor) -> int:
+    if t.dtype == torch.float32:
+        return F32
+    if t.dtype == torch.bfloat16:
+        return BF16
+    raise TypeError(f"unsupported dtype {t.dtype}")
+
+
+def torch_dtype(dt: int) -> torch.dtype:
+    return torch.bfloat16 if dt == BF16 else torch.float32
+
+
+def _stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _ptr(t: Optional[torch.Tensor]) -> Optional[int]:
+    return None if t is None else t.data_ptr()
+
+
+def _require_cuda(*ts):
+    for t in ts:
+        if t is not None and not t.is_cuda:
+            raise RuntimeError("cosyvoice_b200 kernels need CUDA tensors (there is no CPU path)")
+
+
+def gemm_op(plan: TapPlan, A: torch.Tensor, lay: SeqLayout, out0: torch.Tensor, *, engine: int,
+            a_rows: Optional[int] = None, a_cols: Optional[int] = None, seq_len: Optional[torch.Tensor] = None,
+            out_limit: Optional[torch.Tensor] = None, bias: bool = True, seq_bias: Optional[torch.Tensor] = None,
+            act: int = _lib.ACT_NONE, act_alpha: Optional[torch.Tensor] = None, act_slope: float = 0.0,
+            res: Optional[torch.Tensor] = None, out_scale: float = 1.0, accumulate: bool = False,
+            out1: Optional[torch.Tensor] = None, out1_mode: int = _lib.OUT1_NONE,
+            out1_alpha: Optional[torch.Tensor] = None, out1_slope: float = 0.0,
+            gn_stats: Optional[torch.Tensor] = None) -> Op:
+    """A: 2-D time-major tensor (possibly a column slice view) whose rows follow the layout of the
+    INPUT signal; `lay` is the M-space layout (output rows / n_phase).  out0/out1/res: 2-D tensors
+    whose row r, column block [phase*phase_col, +N) receive M-row r of that phase."""
+    _require_cuda(A, out0, plan.W)
+    assert A.dim() == 2 and A.stride(1) == 1 and out0.dim() == 2 and out0.stride(1) == 1
+    g = _lib.Gemm()
+    grp = plan.in_group
+    lda = A.stride(0) * grp
+    g.A, g.W = A.data_ptr(), plan.W.data_ptr()
+    g.tile_seq, g.tile_row0 = lay.tile_seq.data_ptr(), lay.tile_row0.data_ptr()
+    g.seq_len = (seq_len if seq_len is not None else lay.seq_len).data_ptr()
+    g.out_limit = _ptr(out_limit)
+    g.lda = lda
+    g.a_rows = a_rows if a_rows is not None else A.shape[0] // grp
+    g.a_cols = a_cols if a_cols is not None else (A.shape[1] if grp == 1 else lda)
+    g.n_pad, g.N, g.n_phase, g.n_seg, g.seg_len = plan.n_pad, plan.N, plan.n_phase, plan.n_seg, plan.seg_len
+    g.dt = dt_of(A)
+    assert plan.W.dtype == A.dtype, (plan.W.dtype, A.dtype)
+    g.m_tiles = lay.m_tiles
+    g.bn = plan.bn
+    for i, (r, c) in enumerate(zip(plan.seg_row, plan.seg_col)):
+        g.seg_row[i], g.seg_col[i] = r, c
+    e = g.epi
+    e.bias = _ptr(plan.bias) if bias else None
+    e.seq_bias = _ptr(seq_bias)
+    e.seq_bias_ld = seq_bias.stride(0) if seq_bias is not None else 0
+    e.act, e.act_alpha, e.act_slope = act, _ptr(act_alpha), act_slope
+    if res is not None:
+        assert res.stride(1) == 1
+        e.res, e.ldr = res.data_ptr(), res.stride(0) * plan.n_phase
+        e.res_kind = _lib.RES_F32 if res.dtype == torch.float32 else _lib.RES_ACT
+        e.res_dt = dt_of(res)
+    e.out_scale, e.accumulate = out_scale, int(accumulate)
+    # for n_phase > 1 the output buffer [rows*n_phase, ld] is addressed as [rows, n_phase*ld]
+    e.out0, e.ldo0, e.out0_dt = out0.data_ptr(), out0.stride(0) * plan.n_phase, dt_of(out0)
+    e.phase_col = out0.stride(0) if plan.n_phase > 1 else 0
+    if out1 is not None:
+        assert out1.stride(1) == 1 and (plan.n_phase == 1 or out1.stride(0) == out0.stride(0))
+        e.out1, e.ldo1, e.out1_dt = out1.data_ptr(), out1.stride(0) * plan.n_phase, dt_of(out1)
+        e.out1_mode = out1_mode if out1_mode != _lib.OUT1_NONE else _lib.OUT1_COPY
+        e.out1_alpha, e.out1_slope = _ptr(out1_alpha), out1_slope
+    if res is not None and plan.n_phase > 1:
+        assert res.stride(0) == out0.stride(0)
+    if gn_stats is not None:
+        assert gn_stats.dtype == torch.float64
+        e.gn_stats, e.gn_groups = gn_stats.data_ptr(), plan.N // 32
+    lib = _lib.load()
+    keep = (plan, A, lay, out0, seq_len, out_limit, seq_bias, act_alpha, res, out1, out1_alpha, gn_stats)
+
+    def run(_g=g, _keep=keep):
+        _lib.check(lib.cvb200_tapgemm(C.byref(_g), engine, _stream()), "tapgemm")
+    return run
+
+
+def layernorm_op(x, out, gamma, beta, rows: int, eps: float = 1e-5) -> Op:
+    _require_cuda(x, out)
+    lib = _lib.load()
+    args = (x.data_ptr(), x.stride(0), out.data_ptr(), out.stride(0), dt_of(out), gamma.data_ptr(), beta.data_ptr(),
+            rows, x.shape[1], eps)
+    keep = (x, out, gamma, beta)
+    return lambda _k=keep: _lib.check(lib.cvb200_layernorm(*args, _stream()), "layernorm")
+
+
+def norm_mish_op(h, out, gamma, beta, lay: SeqLayout, gn_stats=None, seq_bias=None, eps: float = 1e-5) -> Op:
+    _require_cuda(h, out)
+    lib = _lib.load()
+    args = (h.data_ptr(), h.stride(0), dt_of(h), out.data_ptr(), out.stride(0), dt_of(out), gamma.data_ptr(),
+            beta.data_ptr(), _ptr(gn_stats), _ptr(seq_bias), seq_bias.stride(0) if seq_bias is not None else 0,
+            C.byref(lay.c), h.shape[1], eps)
+    keep = (h, out, gamma, beta, lay, gn_stats, seq_bias)
+    return lambda _k=keep: _lib.check(lib.cvb200_norm_mish(*args, _stream()), "norm_mish")
+
+
+def attention_op(qkv, out, lay: SeqLayout, heads: int, scale: float) -> Op:
+    _require_cuda(qkv, out)
+    lib = _lib.load()
+    assert qkv.dtype == out.dtype
+    args = (qkv.data_ptr(), qkv.stride(0), out.data_ptr(), out.stride(0), dt_of(qkv), C.byref(lay.c), heads, scale)
+    keep = (qkv, out, lay)
+    return lambda _k=keep: _lib.check(lib.cvb200_attention(*args, _stream()), "attention")
+
+
+def time_sinusoid(t: torch.Tensor, out: torch.Tensor, scale: float = 1000.0):
+    _require_cuda(t, out)
+    _lib.check(_lib.load().cvb200_time_sinusoid(t.data_ptr(), t.shape[0], out.shape[1], scale, out.data_ptr(), _stream()),
+               "time_sinusoid")
+
+
+def small_linear(x, W, b, y, pre_act=_lib.ACT_NONE, post_act=_lib.ACT_NONE):
+    _require_cuda(x, W, y)
+    assert x.dtype == W.dtype == y.dtype == torch.float32 and x.is_contiguous() and W.is_contiguous() and y.is_contiguous()
+    _lib.check(_lib.load().cvb200_small_linear(x.data_ptr(), x.shape[0], x.shape[1], W.data_ptr(), _ptr(b), W.shape[0],
+                                               pre_act, post_act, y.data_ptr(), _stream()), "small_linear")
+
+
+def pack_cfg_input(x, mu, cond, spks, out, lay1: SeqLayout):
+    _require_cuda(x, mu, cond, spks, out)
+    _lib.check(_lib.load().cvb200_pack_cfg_input(x.data_ptr(), mu.data_ptr(), cond.data_ptr(), spks.data_ptr(),
+                                                 out.data_ptr(), dt_of(out), C.byref(lay1.c), _stream()), "pack_cfg_input")
+
+
+def euler_cfg(x, v, dt: float, cfg_rate: float):
+    _require_cuda(x, v)
+    _lib.check(_lib.load().cvb200_euler_cfg(x.data_ptr(), v.data_ptr(), x.numel(), dt, cfg_rate, _stream()), "euler_cfg")
+
+
+def rowdot_abs(x, w, b, out, rows: int):
+    _require_cuda(x, w, out)
+    _lib.check(_lib.load().cvb200_rowdot_abs(x.data_ptr(), x.stride(0), dt_of(x), w.data_ptr(), b.data_ptr(), w.numel(),
+                                             out.data_ptr(), rows, _stream()), "rowdot_abs")
+
+
+def sine_source(f0, lay0: SeqLayout, hop: int, sr: float, noise, phase, lin_w, lin_b, prefix_ws, s):
+    _require_cuda(f0, noise, phase, s)
+    assert noise.is_contiguous() and s.is_contiguous() and noise.shape[-1] == s.shape[-1]
+    _lib.check(_lib.load().cvb200_sine_source(f0.data_ptr(), C.byref(lay0.c), hop, sr, noise.data_ptr(), phase.data_ptr(),
+                                              lin_w.data_ptr(), lin_b.data_ptr(), prefix_ws.data_ptr(), s.data_ptr(),
+                                              s.shape[-1], _stream()), "sine_source")
+
+
+def stft16(s, out, lay: SeqLayout):
+    _require_cuda(s, out)
+    _lib.check(_lib.load().cvb200_stft16(s.data_ptr(), s.shape[-1], out.data_ptr(), out.stride(0), dt_of(out),
+                                         C.byref(lay.c), _stream()), "stft16")
+
+
+def istft16(x, lay: SeqLayout, wav, limit: float):
+    _require_cuda(x, wav)
+    assert x.dtype == torch.float32
+    _lib.check(_lib.load().cvb200_istft16(x.data_ptr(), x.stride(0), C.byref(lay.c), wav.data_ptr(), wav.shape[-1], limit,
+                                          _stream()), "istft16")
+
+
+def snake(x, out, alpha, C_: int, lay: SeqLayout):
+    _require_cuda(x, out)
+    _lib.check(_lib.load().cvb200_snake(x.data_ptr(), x.stride(0), dt_of(x), out.data_ptr(), out.stride(0), dt_of(out),
+                                        alpha.data_ptr(), C_, C.byref(lay.c), _stream()), "snake")
+
+
+def reflect_row0(x, C_: int, lay: SeqLayout):
+    _require_cuda(x)
+    _lib.check(_lib.load().cvb200_reflect_row0(x.data_ptr(), x.stride(0), dt_of(x), C_, C.byref(lay.c), _stream()),
+               "reflect_row0")
+
+
+def anti_alias_act_nct(x, up_filter, down_filter, alpha, beta):
+    """Drop-in for the reference's fused operator (alias_free_activation/cuda/activation1d.py:24-28):
+    x [B, C, T] -> [B, C, T], output allocated here like the reference's torch::empty (.cu:224-225)."""
+    _require_cuda(x)
+    x = x.contiguous()
+    y = torch.empty_like(x)
+    B, C_, T = x.shape
+    _lib.check(_lib.load().cvb200_anti_alias_act_nct(x.data_ptr(), y.data_ptr(), dt_of(x), B, C_, T,
+                                                     up_filter.data_ptr(), down_filter.data_ptr(), alpha.data_ptr(),
+                                                     beta.data_ptr(), _stream()), "anti_alias_act_nct")
+    return y
+
+
+def anti_alias_act_rows(x, out, filt, alpha, beta, C_: int, lay: SeqLayout):
+    _require_cuda(x, out)
+    _lib.check(_lib.load().cvb200_anti_alias_act_rows(x.data_ptr(), x.stride(0), dt_of(x), out.data_ptr(), out.stride(0),
+                                                      dt_of(out), filt.data_ptr(), alpha.data_ptr(), beta.data_ptr(), C_,
+                                                      C.byref(lay.c), _stream()), "anti_alias_act_rows")
+
+
+def nct_to_rows(src, out, lay: SeqLayout, C_: Optional[int] = None):
+    """src [B, C, T_max] fp32 (any batch/channel strides, unit time stride) -> rows of `out`."""
+    _require_cuda(src, out)
+    assert src.dtype == torch.float32 and src.stride(2) == 1
+    _lib.check(_lib.load().cvb200_nct_to_rows(src.data_ptr(), src.stride(0), src.stride(1), C_ or src.shape[1],
+                                              out.data_ptr(), out.stride(0), dt_of(out), C.byref(lay.c), _stream()),
+               "nct_to_rows")
+
+
+def rows_to_nct(src, out, lay: SeqLayout, C_: Optional[int] = None):
+    _require_cuda(src, out)
+    assert src.dtype == torch.float32 and out.dtype == torch.float32 and out.stride(2) == 1
+    _lib.check(_lib.load().cvb200_rows_to_nct(src.data_ptr(), src.stride(0), C_ or out.shape[1], out.data_ptr(),
+                                              out.stride(0), out.stride(1), C.byref(lay.c), _stream()), "rows_to_nct")
