@@ -40,6 +40,10 @@ int launch_anti_alias_nct(const void*, void*, int, int, int, int, const float*, 
 }  // namespace cvb
 
 using namespace cvb;
+// the ctypes mirror in cosyvoice_b200/_lib.py relies on this layout (tests/test_lib_cpu.py)
+static_assert(sizeof(cvb200_epilogue) == 128, "cvb200_epilogue layout");
+static_assert(sizeof(cvb200_gemm) == 352, "cvb200_gemm layout");
+static_assert(sizeof(cvb200_layout) == 48, "cvb200_layout layout");
 #define ST(s) reinterpret_cast<cudaStream_t>(s)
 #define NEED(p, what)                                                                    \
   do {                                                                                   \

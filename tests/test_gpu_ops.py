@@ -1,0 +1,337 @@
+"""GPU parity of the individual kernels (through the C ABI) against torch fp32 references."""
+import math
+
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+from cosyvoice_b200 import _lib, ops
+from cosyvoice_b200.layout import SeqLayout
+from cosyvoice_b200.packing import conv1d_plan, conv_transpose1d_plan, linear_plan
+from tapgemm_emul import emulate, from_rows, to_rows
+
+DEV = "cuda"
+
+
+def _sync():
+    torch.cuda.synchronize()
+
+
+def _rel(a, b):
+    return ((a.float() - b.float()).norm() / (b.float().norm() + 1e-12)).item()
+
+
+def _run_gemm(plan, A, lay, N_out_cols, engine, out_dtype=torch.float32, **kw):
+    out = torch.zeros(lay.rows * plan.n_phase, N_out_cols, dtype=out_dtype, device=DEV)
+    ops.gemm_op(plan, A, lay, out, engine=engine, **kw)()
+    _sync()
+    return out
+
+
+@pytest.mark.parametrize("case", ["linear", "conv_k3", "conv_k11_d5", "causal", "stride8", "convT_s8", "convT_s2"])
+def test_tapgemm_simt_fp32_matches_emulation(case):
+    torch.manual_seed(1)
+    lens = [37, 150, 5]
+    cin, cout = 128, 80
+    lay = SeqLayout.build(lens, DEV, halo=32)
+    layc = SeqLayout.build(lens, "cpu", halo=32)
+    if case == "linear":
+        plan_c = linear_plan(torch.randn(cout, cin), torch.randn(cout), torch.float32, "cpu")
+    elif case == "conv_k3":
+        plan_c = conv1d_plan(torch.randn(cout, cin, 3), torch.randn(cout), torch.float32, "cpu")
+    elif case == "conv_k11_d5":
+        plan_c = conv1d_plan(torch.randn(cout, cin, 11), torch.randn(cout), torch.float32, "cpu", dilation=5)
+    elif case == "causal":
+        plan_c = conv1d_plan(torch.randn(cout, cin, 3), torch.randn(cout), torch.float32, "cpu", pad_left=2)
+    elif case == "stride8":
+        plan_c = conv1d_plan(torch.randn(cout, 18, 16), torch.randn(cout), torch.float32, "cpu", stride=8, pad_left=4, c_pad=64)
+    elif case == "convT_s8":
+        plan_c = conv_transpose1d_plan(torch.randn(cin, cout, 16), torch.randn(cout), torch.float32, "cpu", stride=8, padding=4)
+    else:
+        plan_c = conv_transpose1d_plan(torch.randn(cin, cout, 4), torch.randn(cout), torch.float32, "cpu", stride=2, padding=1)
+    import copy
+    plan_g = copy.copy(plan_c)
+    plan_g.W, plan_g.bias = plan_c.W.to(DEV), plan_c.bias.to(DEV)
+    if case == "stride8":
+        lay_in_c = layc.derive(8, 1, [l * 8 + 1 for l in lens])
+        A = torch.randn(lay_in_c.rows, 64)
+        for b in range(3):   # zero the padding rows like every producer does
+            A[lay_in_c.row0[b] + lay_in_c.lens[b]:lay_in_c.row0[b] + lay_in_c.strides[b]] = 0
+    else:
+        A = to_rows([torch.randn(cin, l) for l in lens], layc, cin)
+    want = emulate(plan_c, A, layc)
+    got = _run_gemm(plan_g, A.to(DEV), lay, cout, _lib.ENGINE_SIMT)
+    got = got.reshape(lay.rows, plan_c.n_phase, cout).cpu()
+    assert (got - want).abs().max().item() < 2e-3 * max(1.0, want.abs().max().item())
+
+
+@pytest.mark.parametrize("case", ["linear_256_1536", "linear_1024_256", "conv_k3_320", "conv_k11_d5_128", "convT_s8",
+                                  "final_proj_80", "conv_post_18", "stride8"])
+def test_tapgemm_tcgen05_matches_simt(case):
+    """Same bf16 operands through both engines: the tensor-core path must agree with the FFMA path to fp32
+    accumulation-order noise."""
+    torch.manual_seed(2)
+    lens = [300, 129, 5, 640]
+    bf = torch.bfloat16
+    lay = SeqLayout.build(lens, DEV, halo=32)
+    kw = {}
+    cin = 256
+    if case == "linear_256_1536":
+        plan = linear_plan(torch.randn(1536, 256) * 0.06, None, bf, DEV)
+    elif case == "linear_1024_256":
+        cin = 1024
+        plan = linear_plan(torch.randn(256, 1024) * 0.03, torch.randn(256), bf, DEV)
+        kw = dict(act=_lib.ACT_GELU)
+    elif case == "conv_k3_320":
+        cin = 320
+        plan = conv1d_plan(torch.randn(256, 320, 3) * 0.03, torch.randn(256), bf, DEV)
+    elif case == "conv_k11_d5_128":
+        cin = 128
+        plan = conv1d_plan(torch.randn(128, 128, 11) * 0.03, torch.randn(128), bf, DEV, dilation=5)
+    elif case == "convT_s8":
+        plan = conv_transpose1d_plan(torch.randn(256, 128, 16) * 0.03, torch.randn(128), bf, DEV, stride=8, padding=4)
+    elif case == "final_proj_80":
+        plan = linear_plan(torch.randn(80, 256) * 0.06, torch.randn(80), bf, DEV)
+    elif case == "conv_post_18":
+        cin = 128
+        plan = conv1d_plan(torch.randn(18, 128, 7) * 0.03, torch.randn(18), bf, DEV)
+    else:
+        cin = 64
+        plan = conv1d_plan(torch.randn(256, 18, 16) * 0.1, torch.randn(256), bf, DEV, stride=8, pad_left=4, c_pad=64)
+    if case == "stride8":
+        lay_in = lay.derive(8, 1, [l * 8 + 1 for l in lens])
+        A = torch.randn(lay_in.rows, 64, device=DEV)
+        for b in range(len(lens)):
+            A[lay_in.row0[b] + lay_in.lens[b]:lay_in.row0[b] + lay_in.strides[b]] = 0
+        A[:, 18:] = 0
+    else:
+        A = to_rows([torch.randn(cin, l) for l in lens], SeqLayout.build(lens, "cpu", halo=32), cin).to(DEV)
+    A = A.to(bf)
+    ncol = 32 if plan.N == 18 else plan.N
+    ref = _run_gemm(plan, A, lay, ncol, _lib.ENGINE_SIMT, **kw)
+    got = _run_gemm(plan, A, lay, ncol, _lib.ENGINE_TCGEN05, **kw)
+    err = (got - ref).abs().max().item()
+    assert err < 2e-3 * max(1.0, ref.abs().max().item()), err
+    assert ref.abs().max().item() > 0.1
+
+
+def test_tapgemm_epilogue_features_tcgen05():
+    """bias + residual + scale + accumulate + dual output (snake) + GroupNorm statistics, bf16 engine vs torch."""
+    torch.manual_seed(3)
+    bf = torch.bfloat16
+    lens = [200, 77]
+    lay = SeqLayout.build(lens, DEV)
+    layc = SeqLayout.build(lens, "cpu")
+    w, b = torch.randn(256, 256, 3) * 0.04, torch.randn(256)
+    plan = conv1d_plan(w, b, bf, DEV)
+    xs = [torch.randn(256, l) for l in lens]
+    A = to_rows(xs, layc, 256).to(DEV).to(bf)
+    res = torch.randn(lay.rows, 256, device=DEV)
+    out0 = torch.randn(lay.rows, 256, device=DEV)
+    prev = out0.clone()
+    out1 = torch.zeros(lay.rows, 256, device=DEV, dtype=bf)
+    alpha = (1 + 0.3 * torch.randn(256)).to(DEV)
+    stats = torch.zeros(2, 8, 2, dtype=torch.float64, device=DEV)
+    ops.gemm_op(plan, A, lay, out0, engine=_lib.ENGINE_TCGEN05, res=res, out_scale=0.5, accumulate=True, out1=out1,
+                out1_mode=_lib.OUT1_SNAKE, out1_alpha=alpha, gn_stats=stats)()
+    _sync()
+    for bi, l in enumerate(lens):
+        r0 = lay.row0[bi]
+        xa = A[r0:r0 + l].float().t()[None]
+        conv = F.conv1d(xa, plan.W[0].float().reshape(256, 3, 256).permute(0, 2, 1).contiguous(), b.to(DEV), padding=1)[0].t()
+        want = (conv + res[r0:r0 + l]) * 0.5 + prev[r0:r0 + l]
+        assert (out0[r0:r0 + l] - want).abs().max().item() < 5e-3
+        sn = want + torch.sin(want * alpha) ** 2 / (alpha + 1e-9)
+        assert (out1[r0:r0 + l].float() - sn).abs().max().item() < 0.05
+        assert out0[r0 + l:r0 + lay.strides[bi]].abs().max().item() == 0
+        g = want.reshape(l, 8, 32)
+        s_want = g.sum(dim=(0, 2)).double()
+        q_want = (g * g).sum(dim=(0, 2)).double()
+        assert (stats[bi, :, 0] - s_want).abs().max().item() < 1e-2 * max(1.0, s_want.abs().max().item())
+        assert (stats[bi, :, 1] - q_want).abs().max().item() < 1e-3 * q_want.abs().max().item()
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_layernorm_and_norm_mish(dtype):
+    torch.manual_seed(4)
+    lens = [50, 131]
+    lay = SeqLayout.build(lens, DEV)
+    X = torch.randn(lay.rows, 256, device=DEV) * 2 + 0.5
+    g, b = (1 + 0.1 * torch.randn(256)).to(DEV), (0.1 * torch.randn(256)).to(DEV)
+    out = torch.zeros(lay.rows, 256, device=DEV, dtype=dtype)
+    ops.layernorm_op(X, out, g, b, lay.rows)()
+    _sync()
+    want = F.layer_norm(X, (256,), g, b)
+    tol = 1e-4 if dtype == torch.float32 else 3e-2
+    assert (out.float() - want).abs().max().item() < tol
+    # per-row LayerNorm + Mish + time bias (causal Block1D)
+    h = X.to(dtype)
+    tb = torch.randn(2, 512, device=DEV)[:, 256:]
+    ops.norm_mish_op(h, out, g, b, lay, seq_bias=tb)()
+    _sync()
+    for bi, l in enumerate(lens):
+        r0 = lay.row0[bi]
+        w_ = F.mish(F.layer_norm(h[r0:r0 + l].float(), (256,), g, b)) + tb[bi]
+        assert (out[r0:r0 + l].float() - w_).abs().max().item() < tol
+        assert out[r0 + l:r0 + lay.strides[bi]].abs().max().item() == 0
+    # GroupNorm(8) variant with statistics supplied
+    stats = torch.zeros(2, 8, 2, dtype=torch.float64, device=DEV)
+    for bi, l in enumerate(lens):
+        r0 = lay.row0[bi]
+        gq = h[r0:r0 + l].double().reshape(l, 8, 32)
+        stats[bi, :, 0] = gq.sum(dim=(0, 2))
+        stats[bi, :, 1] = (gq * gq).sum(dim=(0, 2))
+    ops.norm_mish_op(h, out, g, b, lay, gn_stats=stats)()
+    _sync()
+    for bi, l in enumerate(lens):
+        r0 = lay.row0[bi]
+        w_ = F.mish(F.group_norm(h[r0:r0 + l].float().t()[None], 8, g, b))[0].t()
+        assert (out[r0:r0 + l].float() - w_).abs().max().item() < tol
+
+
+@pytest.mark.parametrize("dtype,lens", [(torch.float32, [70, 200]), (torch.bfloat16, [70, 200, 1, 64, 128, 650])])
+def test_attention(dtype, lens):
+    torch.manual_seed(5)
+    lay = SeqLayout.build(lens, DEV)
+    qkv = (torch.randn(lay.rows, 1536, device=DEV) * 1.5).to(dtype)
+    out = torch.zeros(lay.rows, 512, device=DEV, dtype=dtype)
+    ops.attention_op(qkv, out, lay, 8, 0.125)()
+    _sync()
+    for bi, l in enumerate(lens):
+        r0 = lay.row0[bi]
+        x = qkv[r0:r0 + l].float()
+        q, k, v = (x[:, i * 512:(i + 1) * 512].reshape(l, 8, 64).transpose(0, 1) for i in range(3))
+        want = torch.softmax(q @ k.transpose(1, 2) * 0.125, -1) @ v
+        want = want.transpose(0, 1).reshape(l, 512)
+        err = (out[r0:r0 + l].float() - want).abs().max().item()
+        assert err < (1e-4 if dtype == torch.float32 else 3e-2), (bi, l, err)
+
+
+def test_time_embedding_path():
+    torch.manual_seed(6)
+    t = torch.tensor([0.0, 0.1, 0.7, 1.0], device=DEV)
+    out = torch.zeros(4, 320, device=DEV)
+    ops.time_sinusoid(t, out)
+    half = 160
+    k = math.log(10000) / (half - 1)
+    e = 1000.0 * t[:, None] * torch.exp(torch.arange(half, device=DEV).float() * -k)[None]
+    want = torch.cat([e.sin(), e.cos()], -1)
+    _sync()
+    assert (out - want).abs().max().item() < 2e-3        # sin/cos of arguments up to 1000 rad
+    W, b = torch.randn(1024, 320, device=DEV) * 0.05, torch.randn(1024, device=DEV)
+    y = torch.zeros(4, 1024, device=DEV)
+    ops.small_linear(want.contiguous(), W, b, y, post_act=_lib.ACT_SILU)
+    _sync()
+    assert (y - F.silu(F.linear(want, W, b))).abs().max().item() < 1e-4
+    W2 = torch.randn(512, 1024, device=DEV) * 0.03
+    y2 = torch.zeros(4, 512, device=DEV)
+    ops.small_linear(y, W2, None, y2, pre_act=_lib.ACT_MISH)
+    _sync()
+    assert (y2 - F.linear(F.mish(y), W2)).abs().max().item() < 1e-4
+
+
+def test_pack_cfg_and_euler():
+    torch.manual_seed(7)
+    lens = [33, 140]
+    lay = SeqLayout.build(lens, DEV)
+    R = lay.rows
+    x, mu, cond = (torch.randn(R, 80, device=DEV) for _ in range(3))
+    spks = torch.randn(2, 80, device=DEV)
+    out = torch.full((2 * R, 320), 7.0, device=DEV)
+    ops.pack_cfg_input(x, mu, cond, spks, out, lay)
+    _sync()
+    for bi, l in enumerate(lens):
+        r0 = lay.row0[bi]
+        want_c = torch.cat([x[r0:r0 + l], mu[r0:r0 + l], spks[bi][None].expand(l, -1), cond[r0:r0 + l]], 1)
+        assert torch.equal(out[r0:r0 + l], want_c)
+        want_u = torch.cat([x[r0:r0 + l], torch.zeros(l, 240, device=DEV)], 1)
+        assert torch.equal(out[R + r0:R + r0 + l], want_u)
+        assert out[r0 + l:r0 + lay.strides[bi]].abs().max().item() == 0
+    v = torch.randn(2 * R, 80, device=DEV)
+    x0 = x.clone()
+    ops.euler_cfg(x, v, 0.05, 0.7)
+    _sync()
+    want = x0 + 0.05 * (1.7 * v[:R] - 0.7 * v[R:])
+    assert (x - want).abs().max().item() < 1e-5
+
+
+def test_layout_transposes_roundtrip():
+    torch.manual_seed(8)
+    lens = [45, 300, 7]
+    lay = SeqLayout.build(lens, DEV)
+    src = torch.randn(3, 80, 300, device=DEV)
+    rows = torch.zeros(lay.rows, 80, device=DEV)
+    ops.nct_to_rows(src, rows, lay)
+    back = torch.zeros_like(src)
+    ops.rows_to_nct(rows, back, lay)
+    _sync()
+    for bi, l in enumerate(lens):
+        assert torch.equal(back[bi, :, :l], src[bi, :, :l])
+        assert torch.equal(rows[lay.row0[bi]:lay.row0[bi] + l], src[bi, :, :l].t())
+        assert rows[lay.row0[bi] + l:lay.row0[bi] + lay.strides[bi]].abs().max().item() == 0
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_anti_alias_activation_nct_matches_reference_golden(golden_dir, dtype):
+    """Drop-in for the reference's fwd_cuda: checked against the output of the reference's torch Activation1d."""
+    import os
+    d = torch.load(os.path.join(golden_dir, "act1d.pt"), weights_only=True)
+    y = ops.anti_alias_act_nct(d["x"].to(DEV).to(dtype), d["up_filter"].to(DEV), d["down_filter"].to(DEV),
+                               d["alpha"].to(DEV), d["beta"].to(DEV))
+    _sync()
+    tol = 5e-6 if dtype == torch.float32 else 5e-2
+    assert (y.float().cpu() - d["y"]).abs().max().item() < tol
+    # longer, strip-crossing rows against the oracle
+    from oracle import bigvgan_ref
+    g = torch.Generator().manual_seed(9)
+    x = torch.randn(2, 5, 700, generator=g) * 2
+    al, be = torch.randn(5, generator=g) * 0.3, torch.randn(5, generator=g) * 0.3
+    filt = bigvgan_ref.kaiser_sinc_filter()
+    want = bigvgan_ref.anti_alias_act(x, al, be, filt)
+    y = ops.anti_alias_act_nct(x.to(DEV).to(dtype), filt.to(DEV), filt.to(DEV), al.to(DEV), be.to(DEV))
+    assert (y.float().cpu() - want).abs().max().item() < (1e-5 if dtype == torch.float32 else 6e-2)
+    # empty input is a silent no-op like the reference (.cu:195-198)
+    e = ops.anti_alias_act_nct(torch.zeros(1, 4, 0, device=DEV), filt.to(DEV), filt.to(DEV), al[:4].to(DEV), be[:4].to(DEV))
+    assert e.shape == (1, 4, 0)
+
+
+def test_anti_alias_activation_rows_varlen():
+    from oracle import bigvgan_ref
+    g = torch.Generator().manual_seed(10)
+    lens, Cc = [150, 64, 3], 96
+    lay = SeqLayout.build(lens, DEV)
+    layc = SeqLayout.build(lens, "cpu")
+    xs = [torch.randn(Cc, l, generator=g) * 2 for l in lens]
+    al, be = torch.randn(Cc, generator=g) * 0.3, torch.randn(Cc, generator=g) * 0.3
+    filt = bigvgan_ref.kaiser_sinc_filter()
+    A = to_rows(xs, layc, Cc).to(DEV)
+    out = torch.full((lay.rows, Cc), 5.0, device=DEV)
+    ops.anti_alias_act_rows(A, out, filt.to(DEV), al.to(DEV), be.to(DEV), Cc, lay)
+    _sync()
+    got = from_rows(out.cpu(), layc, Cc)
+    for b, x in enumerate(xs):
+        want = bigvgan_ref.anti_alias_act(x[None], al, be, filt)[0]
+        assert (got[b] - want).abs().max().item() < 1e-5, b
+        assert out[lay.row0[b] + lens[b]:lay.row0[b] + lay.strides[b]].abs().max().item() == 0
+
+
+def test_snake_and_reflect():
+    torch.manual_seed(11)
+    lens = [40, 7]
+    lay = SeqLayout.build(lens, DEV)
+    x = torch.randn(lay.rows, 64, device=DEV)
+    al = (1 + 0.3 * torch.randn(64)).to(DEV)
+    out = torch.zeros(lay.rows, 64, device=DEV, dtype=torch.bfloat16)
+    ops.snake(x, out, al, 64, lay)
+    _sync()
+    for b, l in enumerate(lens):
+        r0 = lay.row0[b]
+        want = x[r0:r0 + l] + torch.sin(x[r0:r0 + l] * al) ** 2 / (al + 1e-9)
+        assert (out[r0:r0 + l].float() - want).abs().max().item() < 3e-2
+        assert out[r0 + l:r0 + lay.strides[b]].abs().max().item() == 0
+    ops.reflect_row0(x, 64, lay)
+    _sync()
+    for b in range(2):
+        assert torch.equal(x[lay.row0[b]], x[lay.row0[b] + 2])

@@ -1,0 +1,52 @@
+"""No-GPU checks of the C-ABI library: it loads, exports every symbol include/cvb200.h declares, and argument
+validation fails loudly (no compute is launched here)."""
+import os
+import re
+
+import pytest
+import torch
+
+from cosyvoice_b200 import _lib
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+@pytest.fixture(scope="module")
+def lib():
+    if not os.path.exists(_lib.LIB_PATH):
+        from cosyvoice_b200 import build
+        build.build()
+    return _lib.load()
+
+
+def test_header_symbols_are_exported(lib):
+    hdr = open(os.path.join(ROOT, "include", "cvb200.h")).read()
+    hdr = re.sub(r"/\*.*?\*/", "", hdr, flags=re.S)
+    names = set(re.findall(r"\b(cvb200_[a-z0-9_]+)\s*\(", hdr))
+    assert len(names) >= 20
+    for n in names:
+        assert hasattr(lib, n), f"{n} declared in include/cvb200.h but not exported"
+    assert names == set(_lib.exported_symbols())
+
+
+def test_null_arguments_are_rejected_with_message(lib):
+    st = lib.cvb200_layernorm(None, 256, None, 256, 0, None, None, 8, 256, 1e-5, None)
+    assert st == 1
+    assert b"null" in lib.cvb200_last_error()
+    with pytest.raises(RuntimeError, match="null"):
+        _lib.check(st, "layernorm")
+
+
+def test_ops_refuse_cpu_tensors(lib):
+    from cosyvoice_b200 import ops
+    x = torch.zeros(128, 256)
+    with pytest.raises(RuntimeError, match="no CPU path"):
+        ops.layernorm_op(x, x.clone(), torch.ones(256), torch.zeros(256), 128)
+
+
+def test_struct_sizes_match_c_layout():
+    import ctypes as C
+    # 8 pointers + 16 4-byte fields
+    assert C.sizeof(_lib.Epilogue) == 8 * 8 + 16 * 4
+    assert C.sizeof(_lib.Layout) == 4 * 8 + 3 * 4 + 4
+    assert C.sizeof(_lib.Gemm) == 6 * 8 + 11 * 4 + 2 * 2 * 32 + 4 + C.sizeof(_lib.Epilogue)
