@@ -1,0 +1,292 @@
+#!/usr/bin/env python
+"""Benchmark of the hot path: CosyVoice-300M flow decoder (10 Euler steps, CFG) + HiFT vocoder.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
+
+One "step" = one pass of the hot path over one batch of synthetic utterances (BASELINE.json configs[1]:
+batch 32 x 10 s, 3 s prompt, random-init weights of the named architecture, BF16 operands / FP32 accumulate).
+Prints ONE JSON line (contract in the task statement): `value` = audio-seconds generated per second with the
+inputs resident in HBM, `e2e` = the same through the public batched API with host buffers, `roofline` for the
+dominant kernel (tcgen05 tap GEMM), `cpu_baseline` = the CPU oracle port timed on this box's host cores.
+"""
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+import torch
+
+PROMPT_FRAMES, GEN_FRAMES, HOP, SR = 281, 937, 256, 24000      # 3 s prompt + 10 s generated
+WORKLOAD = "CosyVoice-300M flow (ConditionalCFM, 10 Euler steps, CFG) + HiFT, batch {b} synthetic 10 s utterances (3 s prompt)"
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return dict(tflops=d.get("bf16_tflops_sustained", 1392.1), hbm=d.get("hbm_gbs", 6546.6), src="measured")
+    return dict(tflops=1400.0, hbm=6650.0, src="fallback")
+
+
+class ClockSampler:
+    """nvidia-smi clocks/throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index, self.proc, self.path = index, None, f"/tmp/cvb200_clocks_{os.getpid()}.csv"
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=open(self.path, "w"), stderr=subprocess.DEVNULL)
+        except Exception:
+            self.proc = None
+
+    def stop(self):
+        if self.proc is None:
+            return dict(sm_mhz=None, sm_max_mhz=None, reasons=["nvidia-smi unavailable"])
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for line in open(self.path):
+            f = [x.strip() for x in line.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0]))
+                mx.append(float(f[1]))
+            except ValueError:
+                continue
+            for n, v in zip(names, f[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        # samples under load = upper half (the sampler also sees the idle edges of the region)
+        sm_load = sorted(sm)[len(sm) // 2:] if sm else []
+        return dict(sm_mhz=statistics.median(sm_load) if sm_load else None, sm_max_mhz=max(mx) if mx else None,
+                    reasons=sorted(reasons), samples=len(sm))
+
+
+def audio_seconds(batch: int) -> float:
+    return batch * GEN_FRAMES * HOP / SR
+
+
+# ------------------------------------------------------------------------------------------------ reference arm
+def cpu_reference_pass(n_timesteps: int = 10):
+    """One utterance of the workload through the CPU oracle port (oracle/flow_ref.py + oracle/hift_ref.py: the
+    restatement of the reference's PyTorch modules pinned to the reference's outputs by tests/golden).
+    /root/reference itself (Python + uninstallable deps) cannot travel to the GPU box, hence kind = "port"."""
+    from cosyvoice_b200 import synthetic
+    from oracle import flow_ref, hift_ref
+    fsd, hsd = synthetic.flow_estimator_sd(False, seed=0), synthetic.hift_sd(False, seed=1)
+    mus, spks, conds, zs = synthetic.flow_inputs(1, GEN_FRAMES, PROMPT_FRAMES)
+    T = mus[0].shape[-1]
+
+    def run():
+        with torch.inference_mode():
+            mel = flow_ref.solve_euler(fsd, zs[0], flow_ref.cosine_t_span(n_timesteps), mus[0], torch.ones(1, 1, T),
+                                       spks[0], conds[0])
+            gen = mel[:, :, PROMPT_FRAMES:]
+            pv, nz = hift_ref.draw_source_rng(1, gen.shape[-1] * HOP)
+            wav, _ = hift_ref.hift_inference(hsd, gen, pv, nz)
+        return wav
+    return run
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    torch.set_flush_denormal(True)      # the CFG all-zero branch produces denormals on CPU
+    run = cpu_reference_pass()
+    for _ in range(args.warmup):
+        run()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        run()
+    dt = (time.perf_counter() - t0) / args.steps
+    val = audio_seconds(1) / dt
+    sample = "1 of the batch's utterances per step (T=1218 frames, 10 Euler steps + HiFT), fp32, flush_denormal on"
+    print(json.dumps({
+        "impl": "reference", "metric": "audio_seconds_per_second", "value": val, "unit": "audio-s/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": WORKLOAD.format(b=args.batch), "sample": sample},
+        "cpu_baseline": {"value": val, "unit": "audio-s/s", "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": val, "unit": "audio-s/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }))
+
+
+# ------------------------------------------------------------------------------------------------ B200 arm
+def run_ours(args):
+    import torch.distributed as dist
+    from cosyvoice_b200 import _lib, ops, synthetic
+    from cosyvoice_b200.pipeline import AcousticBackend
+
+    rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: cosyvoice_b200 has no CPU path")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    B, K, W = args.batch, args.steps, max(args.warmup, 1)
+    be = AcousticBackend(synthetic.flow_estimator_sd(False, seed=0), synthetic.hift_sd(False, seed=1), v2=False,
+                         dtype=torch.bfloat16, device=dev)
+    # utterances are independent: rank r owns utterances [r*B, (r+1)*B) -- no collective on the data path
+    mus, spks, conds, zs = synthetic.flow_inputs(B, GEN_FRAMES, PROMPT_FRAMES, first_index=rank * B)
+    prompt_lens = [PROMPT_FRAMES] * B
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, k):
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(k):
+            fn()
+        e1.record()
+        barrier()
+        ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return ms.item() / k
+
+    # ---- resident leg (value)
+    res = be.prepare_resident(mus, spks, conds, zs, prompt_lens)
+    for _ in range(W):
+        be.step_resident(res)
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    l0 = _lib.launch_count()
+    ms_step = timed(lambda: be.step_resident(res), K)
+    eager_launches = _lib.launch_count() - l0
+    clocks = sampler.stop() if rank == 0 else None
+    graph_launches = be.cfm.last_graph_launches
+    wav_resident = res["hprog"].wav
+    assert torch.isfinite(wav_resident).all() and wav_resident.abs().max().item() > 1e-4
+
+    # ---- flow-only timing: ms per CFM step (second half of BASELINE.json's metric)
+    def flow_only():
+        res["st"]["x"].copy_(res["z_rows"])
+        be.cfm.solve_rows(res["lay1"], 10)
+    ms_flow = timed(flow_only, max(1, K // 2))
+
+    # ---- e2e leg: public batched API, pinned host inputs, H2D + D2H inside the timed region
+    pin = lambda seq: [a.contiguous().pin_memory() for a in seq]
+    h_mus, h_spks, h_conds, h_zs = pin(mus), pin(spks), pin(conds), pin(zs)
+    L = GEN_FRAMES * HOP
+    h_out = torch.empty(B, L, dtype=torch.float32).pin_memory()
+
+    def e2e_step():
+        wavs = be.synthesize_batch(h_mus, h_spks, h_conds, h_zs, prompt_lens)
+        for b, w in enumerate(wavs):
+            h_out[b].copy_(w[0], non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+    e2e_step()
+    ms_e2e = timed(e2e_step, max(1, K // 2))
+    h2d = sum(a.numel() * 4 for seq in (h_mus, h_spks, h_conds, h_zs) for a in seq)
+    d2h = h_out.numel() * 4
+
+    # ---- roofline leg: one eager (non-graph) step with CUDA events around every GEMM / attention launch
+    prof = None
+    if rank == 0:
+        be.cfm.use_cuda_graph = False
+        ops.PROFILE = []
+        ea, eb = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        ea.record()
+        be.step_resident(res)
+        eb.record()
+        torch.cuda.synchronize()
+        rec, ops.PROFILE = ops.PROFILE, None
+        be.cfm.use_cuda_graph = True
+        prof = {}
+        for kind, fl, a, b in rec:
+            d = prof.setdefault(kind, dict(launches=0, flops=0, ms=0.0))
+            d["launches"] += 1
+            d["flops"] += fl
+            d["ms"] += a.elapsed_time(b)
+        prof["_step_ms_eager"] = ea.elapsed_time(eb)
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+    pk = peaks()
+    tc = prof.get("tapgemm_tc", dict(launches=0, flops=0, ms=1e-9))
+    achieved = tc["flops"] / (tc["ms"] * 1e-3) / 1e12
+    att = prof.get("attention", dict(launches=0, flops=0, ms=1e-9))
+    total_flops = res["hprog"].flops + 10 * be.cfm.estimator.program(res["lay1"].paired()).flops
+    out = {
+        "metric": "audio_seconds_per_second", "value": world * audio_seconds(B) / (ms_step * 1e-3), "unit": "audio-s/s",
+        "n_gpus": world, "steps": K, "warmup": W, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+        "config": {"workload": WORKLOAD.format(b=B), "global_batch": world * B, "parallelism": f"utterance-sharded x{world}",
+                   "l2": "inputs_larger_than_L2 (multi-GB activation working set per step)",
+                   "ms_per_cfm_step": ms_flow / 10.0, "flow_ms": ms_flow, "algorithmic_tflop_per_step": total_flops / 1e12,
+                   "end_to_end_frac_of_bf16_peak": total_flops / (ms_step * 1e-3) / 1e12 / pk["tflops"]},
+        "e2e": {"value": world * audio_seconds(B) / (ms_e2e * 1e-3), "unit": "audio-s/s", "h2d_bytes_per_step": h2d,
+                "d2h_bytes_per_step": d2h, "ms_per_step": ms_e2e},
+        "gpu_launches": int(eager_launches + K * graph_launches),
+        "clocks": clocks,
+        "roofline": {"bound": "tensor", "kernel": "tapgemm_tc_kernel (tcgen05 implicit-GEMM conv/linear)",
+                     "achieved": achieved, "peak": pk["tflops"], "unit": "TFLOP/s", "frac": achieved / pk["tflops"],
+                     "peak_source": pk["src"] + " bf16_tflops_sustained", "traffic": None,
+                     "launches_per_step": tc["launches"], "kernel_ms_per_step": tc["ms"],
+                     "share_of_eager_step": tc["ms"] / prof["_step_ms_eager"],
+                     "attention": {"kernel": "attention_bf16_kernel (mma.sync flash)", "launches": att["launches"],
+                                   "ms": att["ms"], "achieved_tflops": att["flops"] / (att["ms"] * 1e-3) / 1e12,
+                                   "share_of_eager_step": att["ms"] / prof["_step_ms_eager"]}},
+    }
+    if world == 1:
+        cores = os.cpu_count() or 1
+        torch.set_num_threads(cores)
+        torch.set_flush_denormal(True)
+        run = cpu_reference_pass()
+        t0 = time.perf_counter()
+        run()
+        dt = time.perf_counter() - t0
+        out["cpu_baseline"] = {"value": audio_seconds(1) / dt, "unit": "audio-s/s", "cores": cores, "kind": "port",
+                               "sample": "1 utterance of the batch (T=1218, 10 Euler steps + HiFT), single cold run, fp32, "
+                                         "flush_denormal on"}
+    print(json.dumps(out))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--batch", type=int, default=32)
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -196,8 +196,9 @@ class _Program:
         return s
 
     def _gemm(self, plan: TapPlan, A, L: SeqLayout, out0, **kw):
-        self.ops.append(ops.gemm_op(plan, A, L, out0, engine=self.engine, **kw))
-        self.flops += plan.flops_per_row * sum(L.lens)
+        fl = plan.flops_per_row * sum(L.lens)
+        self.ops.append(ops.gemm_op(plan, A, L, out0, engine=self.engine, flops=fl, **kw))
+        self.flops += fl
 
     def _stage(self, st: dict, A: torch.Tensor, L: SeqLayout, last_copy: torch.Tensor):
         """ResnetBlock1D + 4 BasicTransformerBlocks on layout L; the last FFN epilogue also writes the
@@ -221,8 +222,9 @@ class _Program:
             # components/transformer.py:262-316
             self.ops.append(ops.layernorm_op(X, n, t["ln1"][0], t["ln1"][1], R))
             self._gemm(t["qkv"], n, L, qkv, bias=False)
-            self.ops.append(ops.attention_op(qkv, o, L, HEADS, HEAD_DIM ** -0.5))
-            self.flops += sum(4 * HEADS * HEAD_DIM * l * l for l in L.lens)
+            fl = sum(4 * HEADS * HEAD_DIM * l * l for l in L.lens)
+            self.ops.append(ops.attention_op(qkv, o, L, HEADS, HEAD_DIM ** -0.5, flops=fl))
+            self.flops += fl
             self._gemm(t["out"], o, L, X, res=X)
             self.ops.append(ops.layernorm_op(X, n, t["ln3"][0], t["ln3"][1], R))
             self._gemm(t["ff1"], n, L, f, act=_lib.ACT_GELU)
@@ -347,6 +349,7 @@ class B200ConditionalCFM:
         self.device = estimator.device
         self._graphs: Dict[tuple, tuple] = {}
         self.use_cuda_graph = True
+        self.last_graph_launches = 0        # kernels of libcvb200 inside the last replayed graph
 
     # ---- batched core -----------------------------------------------------------------
     def _state(self, lay1: SeqLayout):
@@ -389,13 +392,16 @@ class B200ConditionalCFM:
             torch.cuda.current_stream().wait_stream(s)
             st["x"].copy_(keep)
             graph = torch.cuda.CUDAGraph()
+            n0 = _lib.launch_count()
             with torch.cuda.graph(graph):
                 self._steps(prog, st, ts, dts)
+            n_launch = _lib.launch_count() - n0
             st["x"].copy_(keep)
             if len(self._graphs) >= 8:
                 self._graphs.pop(next(iter(self._graphs)))
-            g = (graph, prog)
+            g = (graph, prog, n_launch)
             self._graphs[key] = g
+        self.last_graph_launches = g[2]
         g[0].replay()
 
     @torch.inference_mode()

@@ -129,8 +129,9 @@ class _Program:
         self.ops_f0: List[ops.Op] = []
         src, dst = self.mel32, self.fa
         for i, plan in enumerate(w.f0_convs):
-            self.ops_f0.append(ops.gemm_op(plan, src, lay0, dst, engine=simt, act=_lib.ACT_ELU))
-            self.flops += plan.flops_per_row * sum(lay0.lens)
+            fl = plan.flops_per_row * sum(lay0.lens)
+            self.ops_f0.append(ops.gemm_op(plan, src, lay0, dst, engine=simt, act=_lib.ACT_ELU, flops=fl))
+            self.flops += fl
             src, dst = dst, (self.fb if dst is self.fa else self.fa)
         f0_in = src
         self.ops_f0.append(lambda: ops.rowdot_abs(f0_in, w.f0_w, w.f0_b, self.f0, R0))
@@ -181,8 +182,9 @@ class _Program:
         self.ops.append(lambda: ops.istft16(self.cp, lay_f, self.wav, 0.99))
 
     def _gemm(self, plan, A, L, out0, flop_lens=None, **kw):
-        self.ops.append(ops.gemm_op(plan, A, L, out0, engine=self.engine, **kw))
-        self.flops += plan.flops_per_row * sum(flop_lens if flop_lens is not None else L.lens)
+        fl = plan.flops_per_row * sum(flop_lens if flop_lens is not None else L.lens)
+        self.ops.append(ops.gemm_op(plan, A, L, out0, engine=self.engine, flops=fl, **kw))
+        self.flops += fl
 
     def _resblock(self, rb: _ResBlockW, L: SeqLayout, xin, a, b, xr, final: dict):
         """generator.py:91-98.  xin: fp32 block input, a = snake_{alpha1[0]}(xin) in the operand dtype."""

@@ -17,6 +17,23 @@ from .packing import TapPlan
 
 Op = Callable[[], None]
 
+# bench.py's roofline leg: when a list is installed here, every GEMM / attention launch is bracketed by CUDA
+# events on the launching stream and (kind, algorithmic_flops, start, end) is appended to it.
+PROFILE = None
+
+
+def _profiled(kind: str, flops: int, fn):
+    def run():
+        if PROFILE is None:
+            fn()
+            return
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        fn()
+        e1.record()
+        PROFILE.append((kind, flops, e0, e1))
+    return run
+
 
 def dt_of(t: torch.Tensor) -> int:
     if t.dtype == torch.float32:
@@ -51,7 +68,7 @@ def gemm_op(plan: TapPlan, A: torch.Tensor, lay: SeqLayout, out0: torch.Tensor, 
             res: Optional[torch.Tensor] = None, out_scale: float = 1.0, accumulate: bool = False,
             out1: Optional[torch.Tensor] = None, out1_mode: int = _lib.OUT1_NONE,
             out1_alpha: Optional[torch.Tensor] = None, out1_slope: float = 0.0,
-            gn_stats: Optional[torch.Tensor] = None) -> Op:
+            gn_stats: Optional[torch.Tensor] = None, flops: int = 0) -> Op:
     """A: 2-D time-major tensor (possibly a column slice view) whose rows follow the layout of the
     INPUT signal; `lay` is the M-space layout (output rows / n_phase).  out0/out1/res: 2-D tensors
     whose row r, column block [phase*phase_col, +N) receive M-row r of that phase."""
@@ -103,7 +120,7 @@ def gemm_op(plan: TapPlan, A: torch.Tensor, lay: SeqLayout, out0: torch.Tensor, 
 
     def run(_g=g, _keep=keep):
         _lib.check(lib.cvb200_tapgemm(C.byref(_g), engine, _stream()), "tapgemm")
-    return run
+    return _profiled("tapgemm_tc" if engine == _lib.ENGINE_TCGEN05 else "tapgemm_simt", flops, run)
 
 
 def layernorm_op(x, out, gamma, beta, rows: int, eps: float = 1e-5) -> Op:
@@ -125,13 +142,14 @@ def norm_mish_op(h, out, gamma, beta, lay: SeqLayout, gn_stats=None, seq_bias=No
     return lambda _k=keep: _lib.check(lib.cvb200_norm_mish(*args, _stream()), "norm_mish")
 
 
-def attention_op(qkv, out, lay: SeqLayout, heads: int, scale: float) -> Op:
+def attention_op(qkv, out, lay: SeqLayout, heads: int, scale: float, flops: int = 0) -> Op:
     _require_cuda(qkv, out)
     lib = _lib.load()
     assert qkv.dtype == out.dtype
     args = (qkv.data_ptr(), qkv.stride(0), out.data_ptr(), out.stride(0), dt_of(qkv), C.byref(lay.c), heads, scale)
     keep = (qkv, out, lay)
-    return lambda _k=keep: _lib.check(lib.cvb200_attention(*args, _stream()), "attention")
+    return _profiled("attention", flops,
+                     lambda _k=keep: _lib.check(lib.cvb200_attention(*args, _stream()), "attention"))
 
 
 def time_sinusoid(t: torch.Tensor, out: torch.Tensor, scale: float = 1000.0):

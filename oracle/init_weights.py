@@ -1,216 +1,4 @@
-"""Random-init state_dicts with the REFERENCE's parameter names and shapes (TEST INFRASTRUCTURE).
-
-There are no checkpoints on the build or GPU boxes, so tests and benchmarks use random
-weights "of the named architecture".  Key names/shapes are those produced by the reference
-constructors (checked in the build container by `load_state_dict(strict=True)` inside
-oracle/make_golden.py).  Distributions follow the reference initialisers
-(ConditionalDecoder.initialize_weights flow/decoder.py:208-220 = kaiming-normal;
-HiFT init_weights utils/common.py:102-105 = N(0, 0.01); torch defaults elsewhere) except
-that biases / norm affines / snake alphas are made non-trivial so that parity tests
-exercise them.
-"""
-import math
-from typing import Dict
-
-import torch
-
-SD = Dict[str, torch.Tensor]
-
-
-def _g(seed: int) -> torch.Generator:
-    g = torch.Generator(device="cpu")
-    g.manual_seed(seed)
-    return g
-
-
-def _kaiming(g, *shape):
-    fan_in = 1
-    for s in shape[1:]:
-        fan_in *= s
-    return torch.randn(*shape, generator=g) * math.sqrt(2.0 / fan_in)
-
-
-def _uniform_default(g, shape, fan_in):
-    b = 1.0 / math.sqrt(fan_in)
-    return (torch.rand(*shape, generator=g) * 2 - 1) * b
-
-
-def _bias(g, n, std=0.05):
-    return torch.randn(n, generator=g) * std
-
-
-def _affine(g, sd, p_w, p_b, n):
-    sd[p_w] = 1.0 + 0.1 * torch.randn(n, generator=g)
-    sd[p_b] = 0.1 * torch.randn(n, generator=g)
-
-
-# ----------------------------------------------------------------------------- flow estimator
-def flow_estimator_sd(causal: bool, seed: int = 0) -> SD:
-    """ConditionalDecoder(in=320,out=80, channels [256,256] | causal [256], n_blocks 4, mid 12, heads 8x64)."""
-    g = _g(seed)
-    sd: SD = {}
-    C, TE = 256, 1024
-    sd["time_mlp.linear_1.weight"] = _kaiming(g, TE, 320)
-    sd["time_mlp.linear_1.bias"] = _bias(g, TE)
-    sd["time_mlp.linear_2.weight"] = _kaiming(g, TE, TE)
-    sd["time_mlp.linear_2.bias"] = _bias(g, TE)
-    norm_idx = 2 if causal else 1
-
-    def block1d(p, cin):
-        sd[p + "block.0.weight"] = _kaiming(g, C, cin, 3)
-        sd[p + "block.0.bias"] = _bias(g, C)
-        _affine(g, sd, p + f"block.{norm_idx}.weight", p + f"block.{norm_idx}.bias", C)
-
-    def resnet(p, cin):
-        sd[p + "mlp.1.weight"] = _kaiming(g, C, TE)
-        sd[p + "mlp.1.bias"] = _bias(g, C)
-        block1d(p + "block1.", cin)
-        block1d(p + "block2.", C)
-        sd[p + "res_conv.weight"] = _kaiming(g, C, cin, 1)
-        sd[p + "res_conv.bias"] = _bias(g, C)
-
-    def tblock(p):
-        _affine(g, sd, p + "norm1.weight", p + "norm1.bias", C)
-        for n in ("to_q", "to_k", "to_v"):
-            sd[p + f"attn1.{n}.weight"] = _kaiming(g, 512, C)
-        sd[p + "attn1.to_out.0.weight"] = _kaiming(g, C, 512)
-        sd[p + "attn1.to_out.0.bias"] = _bias(g, C)
-        _affine(g, sd, p + "norm3.weight", p + "norm3.bias", C)
-        sd[p + "ff.net.0.proj.weight"] = _kaiming(g, 1024, C)
-        sd[p + "ff.net.0.proj.bias"] = _bias(g, 1024)
-        sd[p + "ff.net.2.weight"] = _kaiming(g, C, 1024)
-        sd[p + "ff.net.2.bias"] = _bias(g, C)
-
-    def stage(p, cin):
-        resnet(p + "0.", cin)
-        for i in range(4):
-            tblock(p + f"1.{i}.")
-
-    n_down = 1 if causal else 2
-    for i in range(n_down):
-        p = f"down_blocks.{i}."
-        stage(p, 320 if i == 0 else C)
-        if i < n_down - 1:      # Downsample1D
-            sd[p + "2.conv.weight"] = _kaiming(g, C, C, 3)
-            sd[p + "2.conv.bias"] = _bias(g, C)
-        else:
-            sd[p + "2.weight"] = _kaiming(g, C, C, 3)
-            sd[p + "2.bias"] = _bias(g, C)
-    for i in range(12):
-        stage(f"mid_blocks.{i}.", C)
-    for i in range(n_down):
-        p = f"up_blocks.{i}."
-        stage(p, 2 * C)
-        if i < n_down - 1:      # Upsample1D: ConvTranspose1d(C, C, 4, 2, 1), weight [Cin, Cout, k]
-            sd[p + "2.conv.weight"] = _uniform_default(g, (C, C, 4), C * 4) * 1.5
-            sd[p + "2.conv.bias"] = _bias(g, C)
-        else:
-            sd[p + "2.weight"] = _kaiming(g, C, C, 3)
-            sd[p + "2.bias"] = _bias(g, C)
-    block1d("final_block.", C)
-    sd["final_proj.weight"] = _kaiming(g, 80, C, 1)
-    sd["final_proj.bias"] = _bias(g, 80)
-    return sd
-
-
-# ----------------------------------------------------------------------------- weight-norm helper
-def _wn(g, sd, p, shape, std=None, fan_in=None, g_jitter=0.1):
-    """old-style weight_norm pair: weight_v [shape], weight_g [shape[0],1,1]."""
-    v = torch.randn(*shape, generator=g) * std if std is not None else _uniform_default(g, shape, fan_in)
-    n = v.reshape(shape[0], -1).norm(dim=1).reshape(-1, 1, 1)
-    sd[p + "weight_v"] = v
-    sd[p + "weight_g"] = n * (1.0 + g_jitter * torch.randn(shape[0], 1, 1, generator=g))
-
-
-def _resblock(g, sd, p, ch, k, std):
-    for name in ("convs1", "convs2"):
-        for i in range(3):
-            _wn(g, sd, f"{p}{name}.{i}.", (ch, ch, k), std=std)
-            sd[f"{p}{name}.{i}.bias"] = _bias(g, ch, 0.02)
-    for name in ("activations1", "activations2"):
-        for i in range(3):
-            sd[f"{p}{name}.{i}.alpha"] = 1.0 + 0.3 * torch.randn(ch, generator=g)
-
-
-# ----------------------------------------------------------------------------- HiFT
-def hift_sd(v2: bool, seed: int = 0) -> SD:
-    """HiFTGenerator(base 512, nb_harmonics 8, rates [8,8] | [8,5,3]) + ConvRNNF0Predictor(1,80,512)."""
-    g = _g(seed)
-    sd: SD = {}
-    rates, ks, src_k = ([8, 5, 3], [16, 11, 7], [7, 7, 11]) if v2 else ([8, 8], [16, 16], [7, 11])
-    sd["m_source.l_linear.weight"] = _uniform_default(g, (1, 9), 9) * 3
-    sd["m_source.l_linear.bias"] = _bias(g, 1)
-    _wn(g, sd, "conv_pre.", (512, 80, 7), fan_in=80 * 7)
-    sd["conv_pre.bias"] = _bias(g, 512)
-    for i, (u, k) in enumerate(zip(rates, ks)):
-        cin, cout = 512 // 2 ** i, 512 // 2 ** (i + 1)
-        _wn(g, sd, f"ups.{i}.", (cin, cout, k), std=0.03)
-        sd[f"ups.{i}.bias"] = _bias(g, cout, 0.02)
-    down = [1] + rates[::-1][:-1]
-    cum = []
-    c = 1
-    for d in down:
-        c *= d
-        cum.append(c)
-    cum = cum[::-1]
-    for i, u in enumerate(cum):
-        ch = 512 // 2 ** (i + 1)
-        k = 1 if u == 1 else 2 * u
-        sd[f"source_downs.{i}.weight"] = _uniform_default(g, (ch, 18, k), 18 * k)
-        sd[f"source_downs.{i}.bias"] = _bias(g, ch, 0.02)
-        _resblock(g, sd, f"source_resblocks.{i}.", ch, src_k[i], std=0.02)
-    for i in range(len(rates)):
-        ch = 512 // 2 ** (i + 1)
-        for j, k in enumerate((3, 7, 11)):
-            _resblock(g, sd, f"resblocks.{i * 3 + j}.", ch, k, std=0.02)
-    ch = 512 // 2 ** len(rates)
-    _wn(g, sd, "conv_post.", (18, ch, 7), std=0.03)
-    sd["conv_post.bias"] = _bias(g, 18, 0.1)
-    # f0 predictor: 5 weight-normed convs + classifier; classifier scaled so f0 spans voiced/unvoiced
-    cin = 80
-    for i in range(5):
-        _wn(g, sd, f"f0_predictor.condnet.{2 * i}.", (512, cin, 3), fan_in=cin * 3)
-        sd[f"f0_predictor.condnet.{2 * i}.bias"] = _bias(g, 512)
-        cin = 512
-    sd["f0_predictor.classifier.weight"] = torch.randn(1, 512, generator=g) * 80.0
-    sd["f0_predictor.classifier.bias"] = torch.full((1,), 30.0)
-    return sd
-
-
-# ----------------------------------------------------------------------------- BigVGAN trunk
-def bigvgan_sd(topology: str = "24k100", seed: int = 0) -> SD:
-    """Trunk parameters only (conv_pre, cond layers, ups, AMP blocks, activation_post, conv_post)."""
-    g = _g(seed)
-    sd: SD = {}
-    if topology == "24k100":
-        in_ch, rates, ks = 100, [4, 4, 2, 2, 2, 2], [8, 8, 4, 4, 4, 4]
-    elif topology == "fork":
-        in_ch, rates, ks = 1024, [8, 5, 3, 2], [16, 11, 7, 2]
-    else:
-        raise ValueError(topology)
-    ch0, spk = 1536, 512
-    _wn(g, sd, "conv_pre.", (ch0, in_ch, 7), fan_in=in_ch * 7)
-    sd["conv_pre.bias"] = _bias(g, ch0)
-    sd["cond_layer.weight"] = _uniform_default(g, (ch0, spk, 1), spk)
-    sd["cond_layer.bias"] = _bias(g, ch0)
-    for i, (u, k) in enumerate(zip(rates, ks)):
-        cin, cout = ch0 // 2 ** i, ch0 // 2 ** (i + 1)
-        _wn(g, sd, f"ups.{i}.0.", (cin, cout, k), std=0.03)
-        sd[f"ups.{i}.0.bias"] = _bias(g, cout, 0.02)
-        sd[f"conds.{i}.weight"] = _uniform_default(g, (cout, spk, 1), spk)
-        sd[f"conds.{i}.bias"] = _bias(g, cout, 0.02)
-        for j, rk in enumerate((3, 7, 11)):
-            p = f"resblocks.{i * 3 + j}."
-            for name in ("convs1", "convs2"):
-                for d in range(3):
-                    _wn(g, sd, f"{p}{name}.{d}.", (cout, cout, rk), std=0.02)
-                    sd[f"{p}{name}.{d}.bias"] = _bias(g, cout, 0.02)
-            for a in range(6):
-                sd[f"{p}activations.{a}.act.alpha"] = 0.3 * torch.randn(cout, generator=g)
-                sd[f"{p}activations.{a}.act.beta"] = 0.3 * torch.randn(cout, generator=g)
-    ch = ch0 // 2 ** len(rates)
-    sd["activation_post.act.alpha"] = 0.3 * torch.randn(ch, generator=g)
-    sd["activation_post.act.beta"] = 0.3 * torch.randn(ch, generator=g)
-    _wn(g, sd, "conv_post.", (1, ch, 7), std=0.01)
-    sd["conv_post.bias"] = _bias(g, 1, 0.02)
-    return sd
+"""Random-init state_dicts with the reference's parameter names (moved to cosyvoice_b200/synthetic.py so that
+bench.py's product arm can build weights "of the named architecture" without importing the oracle).  The
+generator code and its RNG call order are unchanged: tests/golden/*.pt were produced from these seeds."""
+from cosyvoice_b200.synthetic import bigvgan_sd, flow_estimator_sd, hift_sd  # noqa: F401
