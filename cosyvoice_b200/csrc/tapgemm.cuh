@@ -32,11 +32,15 @@ int launch_tapgemm_simt(const GemmParams& p, cudaStream_t stream);
 int launch_tapgemm_tc(const GemmParams& p, cudaStream_t stream);   // dt must be DT_BF16
 
 // ------------------------------------------------------------------------------------ epilogue
-__device__ __forceinline__ float apply_act(int act, float v, float alpha, float slope) {
+// Layout contract (checked by the launchers): every vector the epilogue touches (bias, seq_bias rows,
+// alphas, res, out0, out1) is 16-byte aligned at every chunk start and covers n_pad (>= N, multiple of
+// 16) columns, so each NV-column chunk is handled with 128-bit accesses and no per-element bounds test.
+// All branches below are warp-uniform and sit OUTSIDE the per-element loops: the first version of this
+// epilogue branched per element and its unrolled code overflowed the instruction cache
+// (profiles/r01_tapgemm_v0.md: stall_no_inst dominant, 3 % of tensor peak).
+static __device__ __noinline__ float rare_act(int act, float v, float slope) {
   switch (act) {
-    case ACT_GELU: return gelu_erf(v);
     case ACT_ELU: return eluf(v);
-    case ACT_SNAKE: { float s = __sinf(v * alpha); return v + s * s / (alpha + 1e-9f); }
     case ACT_LRELU: return v > 0.f ? v : v * slope;
     case ACT_MISH: return mishf(v);
     case ACT_TANH: return tanhf(v);
@@ -45,91 +49,160 @@ __device__ __forceinline__ float apply_act(int act, float v, float alpha, float 
   }
 }
 
-// precise snake (sinf) for the fp32 parity path
-__device__ __forceinline__ float snake_precise(float v, float alpha) {
-  float s = sinf(v * alpha);
-  return v + s * s / (alpha + 1e-9f);
+template <int NV> __device__ __forceinline__ void vec_load_f32(const float* __restrict__ p, float (&o)[NV]) {
+#pragma unroll
+  for (int j = 0; j < NV; j += 4) {
+    const float4 t = *reinterpret_cast<const float4*>(p + j);
+    o[j] = t.x; o[j + 1] = t.y; o[j + 2] = t.z; o[j + 3] = t.w;
+  }
+}
+template <int NV> __device__ __forceinline__ void vec_add_f32(const float* p, float (&v)[NV]) {
+#pragma unroll
+  for (int j = 0; j < NV; j += 4) {
+    const float4 t = *reinterpret_cast<const float4*>(p + j);
+    v[j] += t.x; v[j + 1] += t.y; v[j + 2] += t.z; v[j + 3] += t.w;
+  }
+}
+template <int NV> __device__ __forceinline__ void vec_add_bf16(const __nv_bfloat16* p, float (&v)[NV]) {
+  if constexpr (NV % 8 == 0) {
+#pragma unroll
+    for (int j = 0; j < NV; j += 8) {
+      const uint4 u = *reinterpret_cast<const uint4*>(p + j);
+      const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&u);
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const float2 f = __bfloat1622float2(h[i]);
+        v[j + 2 * i] += f.x; v[j + 2 * i + 1] += f.y;
+      }
+    }
+  } else {
+#pragma unroll
+    for (int j = 0; j < NV; j += 4) {
+      const uint2 u = *reinterpret_cast<const uint2*>(p + j);
+      const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&u);
+      const float2 f0 = __bfloat1622float2(h[0]), f1 = __bfloat1622float2(h[1]);
+      v[j] += f0.x; v[j + 1] += f0.y; v[j + 2] += f1.x; v[j + 3] += f1.y;
+    }
+  }
+}
+template <int NV> __device__ __forceinline__ void vec_add_dt(const void* base, size_t idx, int dt, float (&v)[NV]) {
+  if (dt == DT_BF16) vec_add_bf16<NV>(reinterpret_cast<const __nv_bfloat16*>(base) + idx, v);
+  else vec_add_f32<NV>(reinterpret_cast<const float*>(base) + idx, v);
+}
+template <int NV> __device__ __forceinline__ void vec_store_dt(void* base, size_t idx, int dt, const float (&v)[NV]) {
+  if (dt == DT_BF16) {
+    __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(base) + idx;
+    if constexpr (NV % 8 == 0) {
+#pragma unroll
+      for (int j = 0; j < NV; j += 8) {
+        uint4 pk;
+        __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&pk);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) h[i] = __floats2bfloat162_rn(v[j + 2 * i], v[j + 2 * i + 1]);
+        *reinterpret_cast<uint4*>(o + j) = pk;
+      }
+    } else {
+#pragma unroll
+      for (int j = 0; j < NV; j += 4) {
+        uint2 pk;
+        __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&pk);
+        h[0] = __floats2bfloat162_rn(v[j], v[j + 1]);
+        h[1] = __floats2bfloat162_rn(v[j + 2], v[j + 3]);
+        *reinterpret_cast<uint2*>(o + j) = pk;
+      }
+    }
+  } else {
+    float* o = reinterpret_cast<float*>(base) + idx;
+#pragma unroll
+    for (int j = 0; j < NV; j += 4) *reinterpret_cast<float4*>(o + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+  }
 }
 
-// Applies the epilogue to NV consecutive columns [n0, n0+NV) of one output row.
-//   m: global view row, b: sequence, valid: row within valid length (for this phase)
-//   precise: use accurate transcendental functions (fp32 parity mode)
-// Accumulates GroupNorm partial sums for this row into (gsum, gsq) -- all NV columns must lie in
-// one 32-channel group (NV <= 32, n0 % NV == 0).
-template <int NV>
-__device__ __forceinline__ void epi_apply(const Epi& e, int m, int b, bool valid, int phase, int n0, int N,
-                                          float (&v)[NV], bool precise, float& gsum, float& gsq) {
-  const size_t col0 = (size_t)phase * e.phase_col + n0;
+template <int NV, bool PRECISE>
+__device__ __forceinline__ void snake_vec(const float* __restrict__ alpha, const float (&x)[NV], float (&y)[NV]) {
+  float al[NV];
+  vec_load_f32<NV>(alpha, al);
 #pragma unroll
   for (int j = 0; j < NV; ++j) {
-    const int n = n0 + j;
-    float x = v[j];
-    if (n < N && valid) {
-      if (e.bias) x += __ldg(e.bias + n);
-      if (e.seq_bias) x += __ldg(e.seq_bias + (size_t)b * e.seq_bias_ld + n);
-      if (e.act != ACT_NONE) {
-        const float al = e.act == ACT_SNAKE ? __ldg(e.act_alpha + n) : 0.f;
-        x = (precise && e.act == ACT_SNAKE) ? snake_precise(x, al) : apply_act(e.act, x, al, e.act_slope);
-      }
-      if (e.res_kind == RES_F32) x += reinterpret_cast<const float*>(e.res)[(size_t)m * e.ldr + col0 + j];
-      else if (e.res_kind == RES_ACT) x += ld_as_float(e.res, (size_t)m * e.ldr + col0 + j, e.res_dt);
-      x *= e.out_scale;
-      if (e.accumulate) x += ld_as_float(e.out0, (size_t)m * e.ldo0 + col0 + j, e.out0_dt);
-      gsum += x;
-      gsq += x * x;
-    } else {
-      x = 0.f;
-    }
-    v[j] = x;
+    const float s = PRECISE ? sinf(x[j] * al[j]) : __sinf(x[j] * al[j]);
+    y[j] = x[j] + s * s * (PRECISE ? 1.f / (al[j] + 1e-9f) : __fdividef(1.f, al[j] + 1e-9f));
   }
-  // ---- stores (vectorised when the full NV chunk is in range and aligned)
-  const bool full = (n0 + NV <= N);
-  if (e.out0) {
-    if (e.out0_dt == DT_BF16) {
-      __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(e.out0) + (size_t)m * e.ldo0 + col0;
-      if (full && NV % 8 == 0 && ((reinterpret_cast<uintptr_t>(o) & 15) == 0)) {
+}
+
+// Applies the epilogue to the NV consecutive columns [n0, n0+NV) of output row m (phase `phase`) and stores them.
+//   b: sequence of the row, valid: row (and phase) inside the sequence's valid length.
+// GroupNorm partial sums of this chunk are ADDED to (gsum, gsq).
+template <int NV, bool PRECISE>
+__device__ __forceinline__ void epi_apply(const Epi& e, size_t m, int b, bool valid, int phase, int n0, float (&v)[NV],
+                                          float& gsum, float& gsq) {
+  static_assert(NV % 4 == 0, "chunk must be a multiple of 4 columns");
+  if (e.bias) vec_add_f32<NV>(e.bias + n0, v);
+  if (e.seq_bias) vec_add_f32<NV>(e.seq_bias + (size_t)b * e.seq_bias_ld + n0, v);
+  if (e.act != ACT_NONE) {
+    if (e.act == ACT_GELU) {
 #pragma unroll
-        for (int j = 0; j < NV; j += 8) {
-          uint4 pk;
-          __nv_bfloat162 t0 = __floats2bfloat162_rn(v[j], v[j + 1]), t1 = __floats2bfloat162_rn(v[j + 2], v[j + 3]);
-          __nv_bfloat162 t2 = __floats2bfloat162_rn(v[j + 4], v[j + 5]), t3 = __floats2bfloat162_rn(v[j + 6], v[j + 7]);
-          pk.x = *reinterpret_cast<uint32_t*>(&t0); pk.y = *reinterpret_cast<uint32_t*>(&t1);
-          pk.z = *reinterpret_cast<uint32_t*>(&t2); pk.w = *reinterpret_cast<uint32_t*>(&t3);
-          *reinterpret_cast<uint4*>(o + j) = pk;
-        }
-      } else {
-#pragma unroll
-        for (int j = 0; j < NV; ++j) if (n0 + j < N) o[j] = __float2bfloat16_rn(v[j]);
-      }
+      for (int j = 0; j < NV; ++j) v[j] = gelu_erf(v[j]);
+    } else if (e.act == ACT_SNAKE) {
+      snake_vec<NV, PRECISE>(e.act_alpha + n0, v, v);
     } else {
-      float* o = reinterpret_cast<float*>(e.out0) + (size_t)m * e.ldo0 + col0;
-      if (full && NV % 4 == 0 && ((reinterpret_cast<uintptr_t>(o) & 15) == 0)) {
 #pragma unroll
-        for (int j = 0; j < NV; j += 4) *reinterpret_cast<float4*>(o + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
-      } else {
-#pragma unroll
-        for (int j = 0; j < NV; ++j) if (n0 + j < N) o[j] = v[j];
-      }
+      for (int j = 0; j < NV; ++j) v[j] = rare_act(e.act, v[j], e.act_slope);
     }
   }
+  const size_t col = (size_t)phase * e.phase_col + n0;
+  if (e.res_kind == RES_F32) vec_add_f32<NV>(reinterpret_cast<const float*>(e.res) + m * e.ldr + col, v);
+  else if (e.res_kind == RES_ACT) vec_add_dt<NV>(e.res, m * e.ldr + col, e.res_dt, v);
+  if (e.out_scale != 1.f) {
+#pragma unroll
+    for (int j = 0; j < NV; ++j) v[j] *= e.out_scale;
+  }
+  if (e.accumulate) vec_add_dt<NV>(e.out0, m * e.ldo0 + col, e.out0_dt, v);
+  if (!valid) {
+#pragma unroll
+    for (int j = 0; j < NV; ++j) v[j] = 0.f;
+  }
+  if (e.gn_stats) {
+#pragma unroll
+    for (int j = 0; j < NV; ++j) { gsum += v[j]; gsq = fmaf(v[j], v[j], gsq); }
+  }
+  vec_store_dt<NV>(e.out0, m * e.ldo0 + col, e.out0_dt, v);
   if (e.out1_mode != OUT1_NONE) {
+    float y[NV];
+    if (e.out1_mode == OUT1_SNAKE) {
+      snake_vec<NV, PRECISE>(e.out1_alpha + n0, v, y);
+    } else if (e.out1_mode == OUT1_LRELU) {
 #pragma unroll
-    for (int j = 0; j < NV; ++j) {
-      const int n = n0 + j;
-      if (n < N) {
-        float y = v[j];
-        if (valid) {
-          if (e.out1_mode == OUT1_SNAKE) {
-            const float al = __ldg(e.out1_alpha + n);
-            y = precise ? snake_precise(y, al) : apply_act(ACT_SNAKE, y, al, 0.f);
-          } else if (e.out1_mode == OUT1_LRELU) {
-            y = y > 0.f ? y : y * e.out1_slope;
-          }
-        }
-        st_from_float(e.out1, (size_t)m * e.ldo1 + col0 + j, e.out1_dt, y);
-      }
+      for (int j = 0; j < NV; ++j) y[j] = v[j] > 0.f ? v[j] : v[j] * e.out1_slope;
+    } else {
+#pragma unroll
+      for (int j = 0; j < NV; ++j) y[j] = v[j];
     }
+    vec_store_dt<NV>(e.out1, m * e.ldo1 + col, e.out1_dt, y);
   }
+}
+
+// host-side check of the alignment contract above
+inline int check_epilogue_layout(const GemmParams& p) {
+  const Epi& e = p.epi;
+  auto al16 = [](const void* q) { return (reinterpret_cast<uintptr_t>(q) & 15) == 0; };
+  CVB_REQUIRE(p.n_pad % 16 == 0 && p.N <= p.n_pad, "n_pad must be a multiple of 16 covering N");
+  CVB_REQUIRE(e.out0 && al16(e.out0), "out0 must be 16-byte aligned");
+  const int s0 = dtype_size(e.out0_dt);
+  CVB_REQUIRE((e.ldo0 * s0) % 16 == 0 && (e.phase_col * s0) % 16 == 0, "out0 pitch must keep 16-byte alignment");
+  if (e.out1_mode != OUT1_NONE) {
+    const int s1 = dtype_size(e.out1_dt);
+    CVB_REQUIRE(e.out1 && al16(e.out1) && (e.ldo1 * s1) % 16 == 0 && (e.phase_col * s1) % 16 == 0, "out1 alignment");
+    CVB_REQUIRE(e.out1_mode != OUT1_SNAKE || (e.out1_alpha && al16(e.out1_alpha)), "out1_alpha alignment");
+  }
+  if (e.res_kind != RES_NONE) {
+    const int sr = e.res_kind == RES_F32 ? 4 : dtype_size(e.res_dt);
+    CVB_REQUIRE(e.res && al16(e.res) && (e.ldr * sr) % 16 == 0 && (e.phase_col * sr) % 16 == 0, "res alignment");
+  }
+  CVB_REQUIRE(!e.bias || al16(e.bias), "bias must be 16-byte aligned (and padded to n_pad)");
+  CVB_REQUIRE(!e.seq_bias || (al16(e.seq_bias) && e.seq_bias_ld % 4 == 0), "seq_bias alignment");
+  CVB_REQUIRE(e.act != ACT_SNAKE || (e.act_alpha && al16(e.act_alpha)), "act_alpha alignment");
+  CVB_REQUIRE(!e.gn_stats || (p.N % 32 == 0 && e.gn_groups == p.N / 32), "GroupNorm statistics need N % 32 == 0");
+  return CVB_OK;
 }
 
 }  // namespace cvb

@@ -72,14 +72,14 @@ __global__ void __launch_bounds__(NT) tapgemm_simt_kernel(const GemmParams p) {
   const int n0 = nt * BN + tx * 4;
   const int slen = p.seq_len[b];
   const int olim = p.out_limit ? p.out_limit[b] : slen * p.n_phase;
-  const bool precise = (p.dt == DT_F32);
   float gsum = 0.f, gsq = 0.f;
-  if (n0 < p.N) {
+  if (n0 < p.n_pad) {
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
       const int lrow = lrow0 + ty * 8 + i;
       const bool valid = lrow < slen && (lrow * p.n_phase + phase) < olim;
-      epi_apply<4>(p.epi, m0 + ty * 8 + i, b, valid, phase, n0, p.N, acc[i], precise, gsum, gsq);
+      if (p.dt == DT_F32) epi_apply<4, true>(p.epi, (size_t)(m0 + ty * 8 + i), b, valid, phase, n0, acc[i], gsum, gsq);
+      else epi_apply<4, false>(p.epi, (size_t)(m0 + ty * 8 + i), b, valid, phase, n0, acc[i], gsum, gsq);
     }
   }
   if (p.epi.gn_stats) {
@@ -105,7 +105,8 @@ int launch_tapgemm_simt(const GemmParams& p, cudaStream_t stream) {
   CVB_REQUIRE(p.seg_len % BK == 0, "seg_len must be a multiple of 16");
   CVB_REQUIRE(p.n_phase * p.n_seg <= MAX_SEGS, "too many segments");
   CVB_REQUIRE(p.m_tiles > 0, "empty problem");
-  dim3 grid(p.m_tiles, ceil_div(p.N, BN), p.n_phase);
+  CVB_TRY(check_epilogue_layout(p));
+  dim3 grid(p.m_tiles, ceil_div(p.n_pad, BN), p.n_phase);
   if (p.dt == DT_BF16) tapgemm_simt_kernel<__nv_bfloat16><<<grid, NT, 0, stream>>>(p);
   else tapgemm_simt_kernel<float><<<grid, NT, 0, stream>>>(p);
   CVB_LAUNCH_CHECK();

@@ -26,20 +26,25 @@ constexpr int SMEM_BYTES = 1024 + STAGES * (A_STAGE_BYTES + B_STAGE_BYTES) + BAR
 constexpr int NUM_THREADS = 192;
 constexpr int TMEM_COLS = 512;
 
+// One accumulator row (this thread's TMEM lane) of a tile: NV columns at a time.
 template <int NV>
-__device__ __forceinline__ void epilogue_chunks(const GemmParams& p, uint32_t taddr, int bn, int n_base, int m, int b,
-                                                bool valid, int phase, float (&gs)[8], float (&gq)[8]) {
+__device__ __forceinline__ void epilogue_chunks(const GemmParams& p, uint32_t taddr, int bn, int n_base, size_t m, int b,
+                                                bool valid, int phase, int lane) {
+  float gs = 0.f, gq = 0.f;
   for (int c = 0; c < bn; c += NV) {
     float v[NV];
     if constexpr (NV == 32) ptx::tmem_ld32(taddr + c, v);
     else ptx::tmem_ld16(taddr + c, v);
-    float s = 0.f, q = 0.f;
-    epi_apply<NV>(p.epi, m, b, valid, phase, n_base + c, p.N, v, false, s, q);
-    if (p.epi.gn_stats) {
-      // bn == 256 in this case (host check): chunk c covers group (n_base + c) / 32
-      const int g = ((n_base + c) >> 5) & 7;
-      gs[g] += s;
-      gq[g] += q;
+    epi_apply<NV, false>(p.epi, m, b, valid, phase, n_base + c, v, gs, gq);
+    if (p.epi.gn_stats && ((c + NV) & 31) == 0) {
+      // one 32-channel GroupNorm group finished: reduce over the warp's 32 rows, one atomic pair per warp
+      const float s = warp_sum(gs), q = warp_sum(gq);
+      if (lane == 0) {
+        double* dst = p.epi.gn_stats + ((size_t)b * p.epi.gn_groups + ((n_base + c) >> 5)) * 2;
+        atomicAdd(dst, (double)s);
+        atomicAdd(dst + 1, (double)q);
+      }
+      gs = gq = 0.f;
     }
   }
 }
@@ -160,24 +165,10 @@ tapgemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
       ptx::mbar_wait(&tfull[acc], acc_ph);
       ptx::tc_fence_after();
       const uint32_t taddr = tmem_base + ((uint32_t)(lane_grp * 32) << 16) + acc * 256;
-      float gs[8], gq[8];
-#pragma unroll
-      for (int i = 0; i < 8; ++i) gs[i] = gq[i] = 0.f;
-      if ((bn & 31) == 0) epilogue_chunks<32>(p, taddr, bn, nt * bn, m, b, valid, phase, gs, gq);
-      else epilogue_chunks<16>(p, taddr, bn, nt * bn, m, b, valid, phase, gs, gq);
+      if ((bn & 31) == 0) epilogue_chunks<32>(p, taddr, bn, nt * bn, (size_t)m, b, valid, phase, lane);
+      else epilogue_chunks<16>(p, taddr, bn, nt * bn, (size_t)m, b, valid, phase, lane);
       ptx::tc_fence_before();
       ptx::mbar_arrive(&tempty[acc]);
-      if (p.epi.gn_stats) {
-#pragma unroll
-        for (int g = 0; g < 8; ++g) {
-          const float s = warp_sum(gs[g]), q = warp_sum(gq[g]);
-          if (lane == 0 && g < p.epi.gn_groups) {
-            double* dst = p.epi.gn_stats + ((size_t)b * p.epi.gn_groups + g) * 2;
-            atomicAdd(dst, (double)s);
-            atomicAdd(dst + 1, (double)q);
-          }
-        }
-      }
       acc ^= 1;
       if (acc == 0) acc_ph ^= 1;
     }
@@ -247,7 +238,8 @@ int launch_tapgemm_tc(const GemmParams& p, cudaStream_t stream) {
   CVB_REQUIRE(p.n_phase * p.n_seg <= MAX_SEGS, "too many segments");
   CVB_REQUIRE(p.m_tiles > 0, "empty problem");
   CVB_REQUIRE(p.bn >= 16 && p.bn <= 256 && p.bn % 16 == 0 && p.n_pad % p.bn == 0, "bad N tile");
-  CVB_REQUIRE(!p.epi.gn_stats || (p.bn == 256 && p.N == 256), "GroupNorm statistics need N == bn == 256");
+  CVB_REQUIRE(!p.epi.gn_stats || p.bn % 32 == 0, "GroupNorm statistics need bn % 32 == 0");
+  CVB_TRY(check_epilogue_layout(p));
   static std::once_flag attr_once;
   static cudaError_t attr_err = cudaSuccess;
   std::call_once(attr_once, [] {

@@ -112,6 +112,8 @@ def build_plan(phases: List[List[Atom]], N: int, c_pad: int, bias: Optional[torc
             seg_col.append(0)
             s += 1
     assert all(-32768 <= v < 32768 for v in seg_row + seg_col)
+    if bias is not None:                      # the epilogue reads whole 16-column chunks: pad to n_pad
+        bias = torch.cat([bias.detach().float().cpu().reshape(-1), torch.zeros(n_pad - N)])
     return TapPlan(W=W.to(device=device, dtype=dtype).contiguous(),
                    bias=None if bias is None else bias.detach().float().to(device).contiguous(),
                    N=N, n_pad=n_pad, n_phase=n_phase, n_seg=n_seg, seg_len=seg_len, bn=_choose_bn(n_pad),

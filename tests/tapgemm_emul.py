@@ -30,7 +30,7 @@ def emulate(plan, A, lay, seq_len=None, out_limit=None, a_rows=None, a_cols=None
                 slab[ok, :c_hi - c] = Av[src[ok], c:c_hi]
             D[:, p] += slab @ W[p, :plan.N, s * plan.seg_len:(s + 1) * plan.seg_len].t()
     if plan.bias is not None:
-        D += plan.bias.float().cpu().reshape(1, 1, -1)
+        D += plan.bias.float().cpu()[:plan.N].reshape(1, 1, -1)
     slen = lay.lens if seq_len is None else [int(v) for v in seq_len]
     for b in range(lay.n_seq):
         olim = slen[b] * plan.n_phase if out_limit is None else int(out_limit[b])
