@@ -233,13 +233,17 @@ class _Program:
             else:
                 self._gemm(t["ff2"], f, L, X, res=X)
 
-    def run_time_embedding(self):
-        """t [S] (self.t) -> per-resnet time biases (flow/decoder.py:240-241, components/decoder.py:47,56)."""
+    def run_time_embedding(self, shared: bool = False):
+        """t [S] (self.t) -> per-resnet time biases (flow/decoder.py:240-241, components/decoder.py:47,56).
+        shared=True: every sequence has the same t (the CFM solver): evaluate one row and broadcast it."""
         w = self.w
-        ops.time_sinusoid(self.t, self.tsin)
-        ops.small_linear(self.tsin, w.t_w1, w.t_b1, self.th, post_act=_lib.ACT_SILU)
-        ops.small_linear(self.th, w.t_w2, w.t_b2, self.temb)
-        ops.small_linear(self.temb, w.mlp_w, w.mlp_b, self.tbias, pre_act=_lib.ACT_MISH)
+        n = 1 if shared else self.t.shape[0]
+        ops.time_sinusoid(self.t[:n], self.tsin[:n])
+        ops.small_linear(self.tsin[:n], w.t_w1, w.t_b1, self.th[:n], post_act=_lib.ACT_SILU)
+        ops.small_linear(self.th[:n], w.t_w2, w.t_b2, self.temb[:n])
+        ops.small_linear(self.temb[:n], w.mlp_w, w.mlp_b, self.tbias[:n], pre_act=_lib.ACT_MISH)
+        if shared and self.t.shape[0] > 1:
+            self.tbias[1:].copy_(self.tbias[0:1].expand(self.t.shape[0] - 1, -1))
 
     def run(self):
         if self.gn_stats is not None:
@@ -365,7 +369,7 @@ class B200ConditionalCFM:
     def _steps(self, prog: _Program, st: dict, ts: List[float], dts: List[float]):
         for t, dt in zip(ts, dts):
             prog.t.fill_(t)
-            prog.run_time_embedding()
+            prog.run_time_embedding(shared=True)
             ops.pack_cfg_input(st["x"], st["mu"], st["cond"], st["spks"], prog.A0, st["lay1"])
             prog.run()
             ops.euler_cfg(st["x"], prog.v, dt, self.inference_cfg_rate)
