@@ -1,0 +1,95 @@
+"""Utterance sharding across GPUs: utterances are independent, so the batch is
+partitioned by utterance with NO collective on the data path; NCCL/gloo is used only to gather results.
+
+  cost model   : algorithmic FLOPs of one utterance (SURVEY.md 8d formulas)
+  lpt_assign   : longest-processing-time-first greedy assignment to ranks
+  make_batches : per-rank length-bucketed batches under a row budget (rows = varlen-packed frames)
+  gather_by_index : optional result gather (all_gather of per-utterance tensors, padded)
+"""
+import math
+from typing import Dict, List, Sequence
+
+import torch
+
+
+def flow_flops(T: int, v2: bool = False, n_steps: int = 10) -> float:
+    """Estimator FLOPs per CFG-pair call x steps (measured with FlopCounterMode on the reference)."""
+    if v2:
+        per_call = 264.4e6 * T + 229376.0 * T * T
+    else:
+        per_call = 172.4e6 * T + 4096.0 * (8 * T * T + 56 * math.ceil(T / 2) ** 2)
+    return n_steps * per_call
+
+
+def hift_flops(T_gen: int, v2: bool = False) -> float:
+    return (612.3e6 if v2 else 602.1e6) * T_gen
+
+
+def utterance_cost(total_frames: int, gen_frames: int, v2: bool = False) -> float:
+    return flow_flops(total_frames, v2) + hift_flops(gen_frames, v2)
+
+
+def lpt_assign(costs: Sequence[float], n_ranks: int) -> List[List[int]]:
+    """Greedy LPT: heaviest utterance first onto the least-loaded rank.  Deterministic (ties by index)."""
+    order = sorted(range(len(costs)), key=lambda i: (-costs[i], i))
+    loads = [0.0] * n_ranks
+    out: List[List[int]] = [[] for _ in range(n_ranks)]
+    for i in order:
+        r = min(range(n_ranks), key=lambda k: (loads[k], k))
+        out[r].append(i)
+        loads[r] += costs[i]
+    return out
+
+
+def make_batches(indices: Sequence[int], lens: Sequence[int], row_budget: int = 48 * 1024, align: int = 256,
+                 max_batch: int = 64) -> List[List[int]]:
+    """Group a rank's utterances (sorted by length so strides waste little) into batches whose packed row count
+    (sum of round_up(len + 8, align)) stays under `row_budget`."""
+    idx = sorted(indices, key=lambda i: (lens[i], i))
+    batches, cur, rows = [], [], 0
+    for i in idx:
+        r = (lens[i] + 8 + align - 1) // align * align
+        if cur and (rows + r > row_budget or len(cur) >= max_batch):
+            batches.append(cur)
+            cur, rows = [], 0
+        cur.append(i)
+        rows += r
+    if cur:
+        batches.append(cur)
+    return batches
+
+
+def gather_by_index(local: Dict[int, torch.Tensor], n_total: int, group=None) -> List[torch.Tensor]:
+    """Collect per-utterance 1-D results from all ranks (result gather only; not on the compute path).
+    Works on any backend: lengths first, then one padded all_gather."""
+    import torch.distributed as dist
+    if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) == 1:
+        return [local[i] for i in range(n_total)]
+    world = dist.get_world_size(group)
+    dev = next(iter(local.values())).device if local else torch.device("cpu")
+    lens = torch.zeros(n_total, dtype=torch.int64, device=dev)
+    for i, t in local.items():
+        lens[i] = t.numel()
+    dist.all_reduce(lens, op=dist.ReduceOp.SUM, group=group)
+    owner = torch.zeros(n_total, dtype=torch.int64, device=dev)
+    rank = dist.get_rank(group)
+    for i in local:
+        owner[i] = rank
+    dist.all_reduce(owner, op=dist.ReduceOp.SUM, group=group)
+    per_rank = [int(lens[(owner == r)].sum().item()) for r in range(world)]
+    pad = max(per_rank) if per_rank else 0
+    mine = torch.zeros(pad, dtype=torch.float32, device=dev)
+    off = 0
+    for i in sorted(local):
+        n = local[i].numel()
+        mine[off:off + n] = local[i].reshape(-1).float()
+        off += n
+    bufs = [torch.zeros(pad, dtype=torch.float32, device=dev) for _ in range(world)]
+    dist.all_gather(bufs, mine, group=group)
+    out: List[torch.Tensor] = [None] * n_total
+    offs = [0] * world
+    for i in range(n_total):          # each rank packed its utterances in increasing index order
+        r, n = int(owner[i].item()), int(lens[i].item())
+        out[i] = bufs[r][offs[r]:offs[r] + n]
+        offs[r] += n
+    return out

@@ -162,3 +162,27 @@ def test_inference_signature_and_rng_order(golden_dir):
     want_s = hift_ref.sine_source(sd, f0[:, None].repeat_interleave(gen.hop, dim=-1), u, noise.cpu())
     assert (s.cpu() - want_s).abs().max().item() < 3e-4
     assert wav.abs().max().item() <= 0.99 + 1e-6
+
+
+def test_bigvgan_trunk_matches_reference_golden(golden_dir):
+    """BigVGAN trunk (bigvgan.py:406-436) on the 24 kHz / 100-band topology: fp32 against the reference's own
+    output, bf16 (tcgen05) within the stated looser bound."""
+    from cosyvoice_b200.bigvgan import B200BigVGAN
+    from oracle import bigvgan_ref
+    d = _load(golden_dir, "bigvgan_24k100.pt")
+    sd = init_weights.bigvgan_sd(d["topology"], seed=d["weights_seed"])
+    g32 = B200BigVGAN(sd, d["topology"], dtype=torch.float32, device=DEV)
+    wav = g32.inference(d["feat"], d["spk"]).cpu()
+    assert wav.shape == d["wav"].shape
+    assert (wav - d["wav"]).abs().max().item() < 2e-4
+    gbf = B200BigVGAN(sd, d["topology"], dtype=torch.bfloat16, device=DEV)
+    wavb = gbf.inference(d["feat"], d["spk"]).cpu()
+    assert (wavb - d["wav"]).abs().max().item() < 0.05
+    # ragged batch: second item shorter
+    lens = [9, 5]
+    feat = d["feat"].clone()
+    feat[1, :, 5:] = 0
+    wav_r = g32.inference(feat, d["spk"], lens=lens).cpu()
+    want1 = bigvgan_ref.trunk_forward(sd, feat[1:2, :, :5], d["spk"][1:2], d["topology"])
+    assert (wav_r[1, :want1.shape[-1]] - want1[0]).abs().max().item() < 2e-4
+    assert (wav_r[0] - d["wav"][0]).abs().max().item() < 2e-4
