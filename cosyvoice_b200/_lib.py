@@ -15,6 +15,7 @@ MAX_SEGS = 32
 ACT_NONE, ACT_GELU, ACT_ELU, ACT_SNAKE, ACT_LRELU, ACT_MISH, ACT_TANH, ACT_SILU = range(8)
 RES_NONE, RES_F32, RES_ACT = range(3)
 OUT1_NONE, OUT1_COPY, OUT1_SNAKE, OUT1_LRELU = range(4)
+ATTN_TCGEN05, ATTN_MMA_SYNC = 0, 1
 
 
 class Epilogue(C.Structure):
@@ -55,6 +56,7 @@ SIGNATURES = {
     "cvb200_layernorm": [_P, _I, _P, _I, _I, _P, _P, _I, _I, _F, _P],
     "cvb200_norm_mish": [_P, _I, _I, _P, _I, _I, _P, _P, _P, _P, _I, _LAY, _I, _F, _P],
     "cvb200_attention": [_P, _I, _P, _I, _I, _LAY, _I, _F, _P],
+    "cvb200_attention_ex": [_P, _I, _P, _I, _I, _LAY, _I, _F, _I, _P],
     "cvb200_time_sinusoid": [_P, _I, _I, _F, _P, _P],
     "cvb200_small_linear": [_P, _I, _I, _P, _P, _I, _I, _I, _P, _P],
     "cvb200_pack_cfg_input": [_P, _P, _P, _P, _P, _I, _LAY, _P],

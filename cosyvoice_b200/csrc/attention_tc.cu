@@ -1,0 +1,292 @@
+// tcgen05 / TMEM flash attention for the estimator's transformer blocks (8 heads x 64, bf16 operands).
+//   out[q, h*64+d] = sum_j softmax_j(Q[q,h,:].K[j,h,:] * scale) V[j,h,d],  j over the valid rows of q's sequence
+// Reference: cosyvoice/flow/components/transformer.py:266-271 -> diffusers Attention / AttnProcessor2_0
+// (F.scaled_dot_product_attention with the all-ones additive mask of flow/decoder.py:258 = no mask at B=1).
+//
+// One CTA per (128-query tile, head); 2 CTAs co-resident per SM (256 TMEM columns, 80 KiB smem each) so that one
+// CTA's softmax overlaps the other's MMAs.
+//   warp 0      : TMA producer -- Q tile once, then (K, V) 128-key tiles into a 2-stage ring; Q, K and V are
+//                 128x64 boxes of the SAME time-major qkv buffer (one tensor map, 128B swizzle).
+//   warp 1      : TMEM allocator + single-thread tcgen05.mma issuer
+//                   S[128x128] = Q K^T        (SS, both operands K-major)
+//                   O[128x64] += P V          (A = P from TMEM as packed bf16, B = V tile read MN-major in place:
+//                                              no transposed copy of V is ever made)
+//   warps 2..5  : softmax, one query row per thread (TMEM lane): tcgen05.ld S, running max / sum in registers,
+//                 exp2, pack to bf16, tcgen05.st P; O is rescaled in TMEM only when some row max of the warp moved.
+// TMEM columns: S [0,128) fp32, P [128,192) packed bf16, O [192,256) fp32.
+#include <cuda.h>
+#include <mutex>
+#include "common.cuh"
+#include "ptx.cuh"
+#include "../../include/cvb200.h"
+
+namespace cvb {
+
+using Layout = cvb200_layout;
+
+namespace {
+
+constexpr int HD = 64, BQ = 128, BK = 128;
+constexpr int TILE_BYTES = 128 * 64 * 2;            // 16 KiB
+constexpr int KV_STAGES = 2;
+constexpr int SMEM_BYTES = 1024 + TILE_BYTES * (1 + 2 * KV_STAGES) + 128;
+constexpr int TM_S = 0, TM_P = 128, TM_O = 192, TM_COLS = 256;
+
+// MN-major 128B-swizzled shared-memory operand (V tile: rows = keys (K dim), 64 d (N dim) contiguous = 128 B).
+// 8 K-rows form one 1024-byte swizzle atom: SBO = 1024; a single 64-wide atom along N: LBO unused.
+__device__ __forceinline__ uint64_t make_sw128_mnmajor_desc(uint32_t smem_addr) {
+  uint64_t d = 0;
+  d |= (uint64_t)((smem_addr & 0x3FFFF) >> 4);
+  d |= (uint64_t)(1024 >> 4) << 16;       // LBO
+  d |= (uint64_t)(1024 >> 4) << 32;       // SBO
+  d |= (uint64_t)1 << 46;
+  d |= (uint64_t)2 << 61;
+  return d;
+}
+
+__device__ __forceinline__ uint32_t pack2(float lo, float hi) {
+  __nv_bfloat162 t = __floats2bfloat162_rn(lo, hi);
+  return *reinterpret_cast<uint32_t*>(&t);
+}
+
+__global__ void __launch_bounds__(192, 2)
+attention_tc_kernel(const __grid_constant__ CUtensorMap tm, __nv_bfloat16* __restrict__ out, int ldo, const Layout lay,
+                    int heads, float scale_log2) {
+  const int head = blockIdx.x % heads, tile = blockIdx.x / heads;
+  const int b = __ldg(lay.tile_seq + tile);
+  const int q0 = __ldg(lay.tile_row0 + tile);
+  const int len = __ldg(lay.seq_len + b);
+  if (q0 >= len) return;                                   // padding-only tile (uniform for the CTA)
+  const int seq0 = __ldg(lay.seq_row0 + b);
+  const int nblk = (len + BK - 1) / BK;
+  const int inner = heads * HD;
+
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sQ = smem;
+  uint8_t* sK = smem + TILE_BYTES;                         // [KV_STAGES]
+  uint8_t* sV = sK + KV_STAGES * TILE_BYTES;               // [KV_STAGES]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sV + KV_STAGES * TILE_BYTES);
+  uint64_t* q_full = bars;                                 // 1
+  uint64_t* kv_full = bars + 1;                            // [2]
+  uint64_t* kv_empty = bars + 3;                           // [2]
+  uint64_t* s_full = bars + 5;
+  uint64_t* s_free = bars + 6;
+  uint64_t* p_full = bars + 7;
+  uint64_t* pv_done = bars + 8;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 9);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (threadIdx.x == 0) {
+    ptx::mbar_init(q_full, 1);
+    for (int i = 0; i < KV_STAGES; ++i) { ptx::mbar_init(&kv_full[i], 1); ptx::mbar_init(&kv_empty[i], 1); }
+    ptx::mbar_init(s_full, 1);
+    ptx::mbar_init(s_free, 128);
+    ptx::mbar_init(p_full, 128);
+    ptx::mbar_init(pv_done, 1);
+    ptx::fence_barrier_init();
+    ptx::prefetch_tensormap(&tm);
+  }
+  if (warp == 1) ptx::tmem_alloc(tmem_slot, TM_COLS);
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::tc_fence_after();
+  const uint32_t tmem = *tmem_slot;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      ptx::mbar_arrive_expect_tx(q_full, TILE_BYTES);
+      ptx::tma_load_2d(sQ, &tm, q_full, head * HD, seq0 + q0);
+      for (int j = 0; j < nblk; ++j) {
+        const int st = j % KV_STAGES;
+        ptx::mbar_wait(&kv_empty[st], ((j / KV_STAGES) & 1) ^ 1);
+        ptx::mbar_arrive_expect_tx(&kv_full[st], 2 * TILE_BYTES);
+        ptx::tma_load_2d(sK + st * TILE_BYTES, &tm, &kv_full[st], inner + head * HD, seq0 + j * BK);
+        ptx::tma_load_2d(sV + st * TILE_BYTES, &tm, &kv_full[st], 2 * inner + head * HD, seq0 + j * BK);
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      const uint32_t idesc_qk = ptx::make_idesc_bf16(BQ, BK);                       // 128 x 128, A/B K-major
+      const uint32_t idesc_pv = ptx::make_idesc_bf16(BQ, HD) | (1u << 16);          // 128 x 64, B MN-major
+      const uint32_t q_base = ptx::smem_u32(sQ);
+      ptx::mbar_wait(q_full, 0);
+      auto issue_qk = [&](int j) {
+        const int st = j % KV_STAGES;
+        ptx::mbar_wait(&kv_full[st], (j / KV_STAGES) & 1);
+        if (j > 0) ptx::mbar_wait(s_free, (j - 1) & 1);       // softmax has pulled S(j-1) out of TMEM
+        ptx::tc_fence_after();
+        const uint32_t k_base = ptx::smem_u32(sK + st * TILE_BYTES);
+#pragma unroll
+        for (int k = 0; k < HD / 16; ++k)
+          ptx::umma_ss(tmem + TM_S, ptx::make_sw128_kmajor_desc(q_base + k * 32), ptx::make_sw128_kmajor_desc(k_base + k * 32),
+                       idesc_qk, k != 0);
+        ptx::umma_commit(s_full);
+      };
+      issue_qk(0);
+      for (int j = 0; j < nblk; ++j) {
+        if (j + 1 < nblk) issue_qk(j + 1);
+        const int st = j % KV_STAGES;
+        ptx::mbar_wait(p_full, j & 1);                        // P(j) is in TMEM, O has been rescaled
+        ptx::tc_fence_after();
+        const uint32_t v_base = ptx::smem_u32(sV + st * TILE_BYTES);
+#pragma unroll
+        for (int k = 0; k < BK / 16; ++k)
+          ptx::umma_ts(tmem + TM_O, tmem + TM_P + k * 8, make_sw128_mnmajor_desc(v_base + k * 2048), idesc_pv, (j | k) != 0);
+        ptx::umma_commit(&kv_empty[st]);
+        ptx::umma_commit(pv_done);
+      }
+    }
+  } else {
+    // ------------------------------------------------------------------ softmax + output (warps 2..5)
+    const int lane_grp = warp & 3;
+    const int row = lane_grp * 32 + lane;
+    const uint32_t tbase = tmem + ((uint32_t)(lane_grp * 32) << 16);
+    float m_run = -INFINITY, l_run = 0.f;
+    for (int j = 0; j < nblk; ++j) {
+      ptx::mbar_wait(s_full, j & 1);
+      ptx::tc_fence_after();
+      const int nvalid = len - j * BK;                        // keys of this block inside the sequence
+      // pass 1: row max
+      float mx = m_run;
+#pragma unroll
+      for (int c = 0; c < BK; c += 32) {
+        float v[32];
+        ptx::tmem_ld32(tbase + TM_S + c, v);
+        if (nvalid < BK) {
+#pragma unroll
+          for (int i = 0; i < 32; ++i) if (c + i >= nvalid) v[i] = -INFINITY;
+        }
+#pragma unroll
+        for (int i = 0; i < 32; ++i) mx = fmaxf(mx, v[i]);
+      }
+      const float m_new = mx;
+      const float corr = exp2f((m_run - m_new) * scale_log2);       // first block: exp2(-inf) = 0
+      const bool moved = __any_sync(0xffffffffu, m_new > m_run);
+      m_run = m_new;
+      const float moff = m_new * scale_log2;
+      if (j > 0) ptx::mbar_wait(pv_done, (j - 1) & 1);               // PV(j-1) retired: P and O may be touched
+      ptx::tc_fence_after();
+      // pass 2: p = exp2(s*scale - m*scale), packed to bf16 into the P columns
+      float lsum = 0.f;
+#pragma unroll
+      for (int c = 0; c < BK; c += 32) {
+        float v[32];
+        ptx::tmem_ld32(tbase + TM_S + c, v);
+        uint32_t pk[16];
+#pragma unroll
+        for (int i = 0; i < 32; i += 2) {
+          float p0 = exp2f(fmaf(v[i], scale_log2, -moff));
+          float p1 = exp2f(fmaf(v[i + 1], scale_log2, -moff));
+          if (nvalid < BK) {
+            if (c + i >= nvalid) p0 = 0.f;
+            if (c + i + 1 >= nvalid) p1 = 0.f;
+          }
+          lsum += p0 + p1;
+          pk[i >> 1] = pack2(p0, p1);
+        }
+        ptx::tmem_st16(tbase + TM_P + (c >> 1), pk);
+      }
+      ptx::tc_fence_before();
+      ptx::mbar_arrive(s_free);                                      // S(j) fully consumed
+      l_run = l_run * corr + lsum;
+      if (j > 0 && moved) {                                          // rescale the running output
+#pragma unroll
+        for (int c = 0; c < HD; c += 32) {
+          float o[32];
+          ptx::tmem_ld32(tbase + TM_O + c, o);
+          uint32_t w[32];
+#pragma unroll
+          for (int i = 0; i < 32; ++i) w[i] = __float_as_uint(o[i] * corr);
+          uint32_t lo[16], hi[16];
+#pragma unroll
+          for (int i = 0; i < 16; ++i) { lo[i] = w[i]; hi[i] = w[16 + i]; }
+          ptx::tmem_st16(tbase + TM_O + c, lo);
+          ptx::tmem_st16(tbase + TM_O + c + 16, hi);
+        }
+      }
+      ptx::tmem_wait_st();
+      ptx::tc_fence_before();
+      ptx::mbar_arrive(p_full);
+    }
+    // ---- epilogue: O / l -> bf16
+    ptx::mbar_wait(pv_done, (nblk - 1) & 1);
+    ptx::tc_fence_after();
+    const float inv = 1.f / l_run;
+    const int lrow = q0 + row;
+    __nv_bfloat16* dst = out + (size_t)(seq0 + lrow) * ldo + head * HD;
+#pragma unroll
+    for (int c = 0; c < HD; c += 32) {
+      float o[32];
+      ptx::tmem_ld32(tbase + TM_O + c, o);
+      if (lrow < len) {
+#pragma unroll
+        for (int i = 0; i < 32; i += 8) {
+          uint4 pk;
+          pk.x = pack2(o[i] * inv, o[i + 1] * inv);
+          pk.y = pack2(o[i + 2] * inv, o[i + 3] * inv);
+          pk.z = pack2(o[i + 4] * inv, o[i + 5] * inv);
+          pk.w = pack2(o[i + 6] * inv, o[i + 7] * inv);
+          *reinterpret_cast<uint4*>(dst + c + i) = pk;
+        }
+      }
+    }
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  if (warp == 1) ptx::tmem_dealloc(tmem, TM_COLS);
+}
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* ptr = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &ptr, cudaEnableDefault, &qres) == cudaSuccess &&
+        qres == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(ptr);
+  });
+  return fn;
+}
+
+}  // namespace
+
+int launch_attention_tc(const void* qkv, int ld, void* out, int ldo, const Layout& lay, int heads, float scale,
+                        cudaStream_t st) {
+  CVB_REQUIRE(heads > 0 && ld >= 3 * heads * HD && ldo >= heads * HD, "bad attention shapes");
+  CVB_REQUIRE(ld % 8 == 0 && ldo % 8 == 0, "leading dimensions must keep 16-byte alignment");
+  CVB_REQUIRE((reinterpret_cast<uintptr_t>(qkv) & 15) == 0 && (reinterpret_cast<uintptr_t>(out) & 15) == 0, "alignment");
+  if (lay.rows <= 0) return CVB_OK;
+  EncodeTiledFn fn = encode_fn();
+  CVB_REQUIRE(fn != nullptr, "cuTensorMapEncodeTiled not available from the driver");
+  CUtensorMap tm;
+  cuuint64_t dims[2] = {(cuuint64_t)(3 * heads * HD), (cuuint64_t)lay.rows};
+  cuuint64_t strides[1] = {(cuuint64_t)ld * 2};
+  cuuint32_t box[2] = {64, 128};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = fn(&tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(qkv), dims, strides, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    set_last_error("cuTensorMapEncodeTiled (attention) failed with CUresult " + std::to_string((int)r));
+    return CVB_ERR_CUDA;
+  }
+  static std::once_flag attr_once;
+  static cudaError_t attr_err = cudaSuccess;
+  std::call_once(attr_once, [] {
+    attr_err = cudaFuncSetAttribute(attention_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
+  });
+  CVB_CUDA(attr_err);
+  const int grid = (lay.rows / 128) * heads;
+  attention_tc_kernel<<<grid, 192, SMEM_BYTES, st>>>(tm, reinterpret_cast<__nv_bfloat16*>(out), ldo, lay, heads,
+                                                     scale * 1.4426950408889634f);
+  CVB_LAUNCH_CHECK();
+  return CVB_OK;
+}
+
+}  // namespace cvb

@@ -142,14 +142,15 @@ def norm_mish_op(h, out, gamma, beta, lay: SeqLayout, gn_stats=None, seq_bias=No
     return lambda _k=keep: _lib.check(lib.cvb200_norm_mish(*args, _stream()), "norm_mish")
 
 
-def attention_op(qkv, out, lay: SeqLayout, heads: int, scale: float, flops: int = 0) -> Op:
+def attention_op(qkv, out, lay: SeqLayout, heads: int, scale: float, flops: int = 0,
+                 impl: int = _lib.ATTN_TCGEN05) -> Op:
     _require_cuda(qkv, out)
     lib = _lib.load()
     assert qkv.dtype == out.dtype
-    args = (qkv.data_ptr(), qkv.stride(0), out.data_ptr(), out.stride(0), dt_of(qkv), C.byref(lay.c), heads, scale)
+    args = (qkv.data_ptr(), qkv.stride(0), out.data_ptr(), out.stride(0), dt_of(qkv), C.byref(lay.c), heads, scale, impl)
     keep = (qkv, out, lay)
     return _profiled("attention", flops,
-                     lambda _k=keep: _lib.check(lib.cvb200_attention(*args, _stream()), "attention"))
+                     lambda _k=keep: _lib.check(lib.cvb200_attention_ex(*args, _stream()), "attention"))
 
 
 def time_sinusoid(t: torch.Tensor, out: torch.Tensor, scale: float = 1000.0):

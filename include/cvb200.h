@@ -149,6 +149,12 @@ int cvb200_norm_mish(const void* h, int ldh, int h_dt, void* out, int ldo, int o
  * additive mask of flow/decoder.py:258). */
 int cvb200_attention(const void* qkv, int ld, void* out, int ldo, int dt, const cvb200_layout* lay,
                      int heads, float scale, void* stream);
+/* same, with an explicit kernel choice for bf16: 0 = tcgen05/TMEM flash kernel (default of cvb200_attention),
+ * 1 = warp-level mma.sync flash kernel (kept as the on-device cross-check) */
+#define CVB200_ATTN_TCGEN05 0
+#define CVB200_ATTN_MMA_SYNC 1
+int cvb200_attention_ex(const void* qkv, int ld, void* out, int ldo, int dt, const cvb200_layout* lay,
+                        int heads, float scale, int impl, void* stream);
 
 /* SinusoidalPosEmb(dim, scale 1000): flow/components/decoder.py:18-27.  t [S] -> out [S, dim] */
 int cvb200_time_sinusoid(const float* t, int S, int dim, float scale, float* out, void* stream);

@@ -191,13 +191,15 @@ def test_layernorm_and_norm_mish(dtype):
         assert (out[r0:r0 + l].float() - w_).abs().max().item() < tol
 
 
-@pytest.mark.parametrize("dtype,lens", [(torch.float32, [70, 200]), (torch.bfloat16, [70, 200, 1, 64, 128, 650])])
-def test_attention(dtype, lens):
+@pytest.mark.parametrize("dtype,lens,impl", [(torch.float32, [70, 200], 0),
+                                             (torch.bfloat16, [70, 200, 1, 64, 128, 650], _lib.ATTN_MMA_SYNC),
+                                             (torch.bfloat16, [70, 200, 1, 64, 128, 650, 129, 1218], _lib.ATTN_TCGEN05)])
+def test_attention(dtype, lens, impl):
     torch.manual_seed(5)
     lay = SeqLayout.build(lens, DEV)
     qkv = (torch.randn(lay.rows, 1536, device=DEV) * 1.5).to(dtype)
     out = torch.zeros(lay.rows, 512, device=DEV, dtype=dtype)
-    ops.attention_op(qkv, out, lay, 8, 0.125)()
+    ops.attention_op(qkv, out, lay, 8, 0.125, impl=impl)()
     _sync()
     for bi, l in enumerate(lens):
         r0 = lay.row0[bi]
