@@ -44,6 +44,12 @@ __device__ __forceinline__ uint64_t make_sw128_mnmajor_desc(uint32_t smem_addr) 
   return d;
 }
 
+__device__ __forceinline__ float ex2_approx(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
 __device__ __forceinline__ uint32_t pack2(float lo, float hi) {
   __nv_bfloat162 t = __floats2bfloat162_rn(lo, hi);
   return *reinterpret_cast<uint32_t*>(&t);
@@ -148,7 +154,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tm, __nv_bfloat16* __res
       ptx::tc_fence_after();
       const int nvalid = len - j * BK;                        // keys of this block inside the sequence
       // pass 1: row max
-      float mx = m_run;
+      float mx4[4] = {m_run, m_run, m_run, m_run};                   // independent chains: no 128-long dependency
 #pragma unroll
       for (int c = 0; c < BK; c += 32) {
         float v[32];
@@ -158,17 +164,22 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tm, __nv_bfloat16* __res
           for (int i = 0; i < 32; ++i) if (c + i >= nvalid) v[i] = -INFINITY;
         }
 #pragma unroll
-        for (int i = 0; i < 32; ++i) mx = fmaxf(mx, v[i]);
+        for (int i = 0; i < 32; i += 4) {
+          mx4[0] = fmaxf(mx4[0], v[i]);
+          mx4[1] = fmaxf(mx4[1], v[i + 1]);
+          mx4[2] = fmaxf(mx4[2], v[i + 2]);
+          mx4[3] = fmaxf(mx4[3], v[i + 3]);
+        }
       }
-      const float m_new = mx;
-      const float corr = exp2f((m_run - m_new) * scale_log2);       // first block: exp2(-inf) = 0
+      const float m_new = fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3]));
+      const float corr = ex2_approx((m_run - m_new) * scale_log2);   // first block: exp2(-inf) = 0
       const bool moved = __any_sync(0xffffffffu, m_new > m_run);
       m_run = m_new;
       const float moff = m_new * scale_log2;
       if (j > 0) ptx::mbar_wait(pv_done, (j - 1) & 1);               // PV(j-1) retired: P and O may be touched
       ptx::tc_fence_after();
       // pass 2: p = exp2(s*scale - m*scale), packed to bf16 into the P columns
-      float lsum = 0.f;
+      float ls4[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
       for (int c = 0; c < BK; c += 32) {
         float v[32];
@@ -176,17 +187,18 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tm, __nv_bfloat16* __res
         uint32_t pk[16];
 #pragma unroll
         for (int i = 0; i < 32; i += 2) {
-          float p0 = exp2f(fmaf(v[i], scale_log2, -moff));
-          float p1 = exp2f(fmaf(v[i + 1], scale_log2, -moff));
+          float p0 = ex2_approx(fmaf(v[i], scale_log2, -moff));
+          float p1 = ex2_approx(fmaf(v[i + 1], scale_log2, -moff));
           if (nvalid < BK) {
             if (c + i >= nvalid) p0 = 0.f;
             if (c + i + 1 >= nvalid) p1 = 0.f;
           }
-          lsum += p0 + p1;
+          ls4[(i >> 1) & 3] += p0 + p1;
           pk[i >> 1] = pack2(p0, p1);
         }
         ptx::tmem_st16(tbase + TM_P + (c >> 1), pk);
       }
+      const float lsum = (ls4[0] + ls4[1]) + (ls4[2] + ls4[3]);
       ptx::tc_fence_before();
       ptx::mbar_arrive(s_free);                                      // S(j) fully consumed
       l_run = l_run * corr + lsum;
