@@ -6,7 +6,7 @@
 //              conv padding) and one bn x 64 box of the packed weights, into a 4-stage smem ring.
 //   warp 1   : TMEM allocator + single-thread tcgen05.mma issuer (UMMA 128 x bn x 16, SS operands,
 //              128B-swizzled K-major descriptors), double-buffered accumulators (2 x 256 columns).
-//   warps 2-5: epilogue. tcgen05.ld the accumulator rows, fused bias / time-bias / activation /
+//   warps 2-9: epilogue (two warps per TMEM lane group, column chunks interleaved). tcgen05.ld the accumulator rows, fused bias / time-bias / activation /
 //              residual / scale / accumulate / dual store / GroupNorm statistics (tapgemm.cuh).
 // The epilogue of tile i overlaps the MMAs of tile i+1 through the two TMEM buffers.
 #include <cuda.h>
@@ -23,15 +23,16 @@ constexpr int A_STAGE_BYTES = TILE_M * GEMM_BK * 2;        // 16 KiB
 constexpr int B_STAGE_BYTES = 256 * GEMM_BK * 2;           // 32 KiB (bn <= 256)
 constexpr int BAR_BYTES = 256;
 constexpr int SMEM_BYTES = 1024 + STAGES * (A_STAGE_BYTES + B_STAGE_BYTES) + BAR_BYTES;
-constexpr int NUM_THREADS = 192;
+constexpr int EPI_WARPS = 8;                                 // 2 per TMEM lane group: chunks interleaved between them
+constexpr int NUM_THREADS = 64 + 32 * EPI_WARPS;
 constexpr int TMEM_COLS = 512;
 
 // One accumulator row (this thread's TMEM lane) of a tile: NV columns at a time.
 template <int NV>
 __device__ __forceinline__ void epilogue_chunks(const GemmParams& p, uint32_t taddr, int bn, int n_base, size_t m, int b,
-                                                bool valid, int phase, int lane) {
+                                                bool valid, int phase, int lane, int half) {
   float gs = 0.f, gq = 0.f;
-  for (int c = 0; c < bn; c += NV) {
+  for (int c = half * NV; c < bn; c += (EPI_WARPS / 4) * NV) {
     float v[NV];
     if constexpr (NV == 32) ptx::tmem_ld32(taddr + c, v);
     else ptx::tmem_ld16(taddr + c, v);
@@ -51,7 +52,7 @@ __device__ __forceinline__ void epilogue_chunks(const GemmParams& p, uint32_t ta
 
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 tapgemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW,
-                  const __grid_constant__ GemmParams p) {
+                  const __grid_constant__ GemmParams p, const int resident) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* sA = smem;
@@ -61,13 +62,26 @@ tapgemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
   uint64_t* empty = bars + STAGES;       // [STAGES]
   uint64_t* tfull = bars + 2 * STAGES;   // [2]
   uint64_t* tempty = tfull + 2;          // [2]
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
+  uint64_t* w_full = tempty + 2;         // [1] resident-W mode: the whole weight tile has landed
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(w_full + 1);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int bn = p.bn;
   const int n_tiles = p.n_pad / bn;
-  const int total = p.m_tiles * p.n_phase * n_tiles;
   const int chunks_per_seg = p.seg_len / GEMM_BK;
+  // Work items.  Streaming mode: item -> (m tile, phase, n tile), round-robin over CTAs, A and W boxes stream
+  // through the ring.  Resident mode (the [bn x K] weight tile fits the 128 KiB B region): the CTA owns ONE
+  // (phase, n tile), loads its weights once and streams only A tiles -- 3x less L2->SM traffic for the K=256
+  // projections (QKV, FFN-in), which are otherwise bound by re-fetching W per tile.
+  const int keys = p.n_phase * n_tiles;
+  const int it0 = resident ? (int)blockIdx.x / keys : (int)blockIdx.x;
+  const int it_step = resident ? (int)gridDim.x / keys : (int)gridDim.x;
+  const int it_end = resident ? p.m_tiles : p.m_tiles * keys;
+  const int key_phase = ((int)blockIdx.x % keys) / n_tiles, key_nt = ((int)blockIdx.x % keys) % n_tiles;
+  auto decode = [&](int it, int& mt, int& phase, int& nt) {
+    if (resident) { mt = it; phase = key_phase; nt = key_nt; }
+    else { nt = it % n_tiles; const int rest = it / n_tiles; phase = rest % p.n_phase; mt = rest / p.n_phase; }
+  };
 
   if (threadIdx.x == 0) {
     for (int i = 0; i < STAGES; ++i) {
@@ -76,8 +90,9 @@ tapgemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     }
     for (int i = 0; i < 2; ++i) {
       ptx::mbar_init(&tfull[i], 1);
-      ptx::mbar_init(&tempty[i], 128);
+      ptx::mbar_init(&tempty[i], 32 * EPI_WARPS);
     }
+    ptx::mbar_init(w_full, 1);
     ptx::fence_barrier_init();
     ptx::prefetch_tensormap(&tmA);
     ptx::prefetch_tensormap(&tmW);
@@ -93,21 +108,27 @@ tapgemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     if (lane == 0) {
       int stage = 0;
       uint32_t ph = 0;
-      for (int item = blockIdx.x; item < total; item += gridDim.x) {
-        const int nt = item % n_tiles;
-        const int rest = item / n_tiles;
-        const int phase = rest % p.n_phase;
-        const int mt = rest / p.n_phase;
+      const uint32_t w_box_bytes = bn * GEMM_BK * 2;
+      if (resident && it0 < it_end) {
+        const int kblocks = p.n_seg * chunks_per_seg;
+        ptx::mbar_arrive_expect_tx(w_full, kblocks * w_box_bytes);
+        for (int kb = 0; kb < kblocks; ++kb)
+          ptx::tma_load_2d(sB + kb * w_box_bytes, &tmW, w_full, kb * GEMM_BK, key_phase * p.n_pad + key_nt * bn);
+      }
+      for (int it = it0; it < it_end; it += it_step) {
+        int mt, phase, nt;
+        decode(it, mt, phase, nt);
         const int m0 = mt * TILE_M;
         const int wrow = phase * p.n_pad + nt * bn;
-        const uint32_t tx_bytes = A_STAGE_BYTES + bn * GEMM_BK * 2;
+        const uint32_t tx_bytes = A_STAGE_BYTES + (resident ? 0u : w_box_bytes);
         for (int seg = 0; seg < p.n_seg; ++seg) {
           const int srow = p.seg_row[phase * p.n_seg + seg], scol = p.seg_col[phase * p.n_seg + seg];
           for (int c = 0; c < chunks_per_seg; ++c) {
             ptx::mbar_wait(&empty[stage], ph ^ 1);
             ptx::mbar_arrive_expect_tx(&full[stage], tx_bytes);
             ptx::tma_load_2d(sA + stage * A_STAGE_BYTES, &tmA, &full[stage], scol + c * GEMM_BK, m0 + srow);
-            ptx::tma_load_2d(sB + stage * B_STAGE_BYTES, &tmW, &full[stage], seg * p.seg_len + c * GEMM_BK, wrow);
+            if (!resident)
+              ptx::tma_load_2d(sB + stage * B_STAGE_BYTES, &tmW, &full[stage], seg * p.seg_len + c * GEMM_BK, wrow);
             if (++stage == STAGES) { stage = 0; ph ^= 1; }
           }
         }
@@ -122,7 +143,8 @@ tapgemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
       uint32_t ph = 0;
       int acc = 0;
       uint32_t acc_ph = 0;
-      for (int item = blockIdx.x; item < total; item += gridDim.x) {
+      if (resident && it0 < it_end) ptx::mbar_wait(w_full, 0);
+      for (int it = it0; it < it_end; it += it_step) {
         ptx::mbar_wait(&tempty[acc], acc_ph ^ 1);
         ptx::tc_fence_after();
         const uint32_t d_tmem = tmem_base + acc * 256;
@@ -130,7 +152,7 @@ tapgemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
           ptx::mbar_wait(&full[stage], ph);
           ptx::tc_fence_after();
           const uint32_t a_base = ptx::smem_u32(sA + stage * A_STAGE_BYTES);
-          const uint32_t b_base = ptx::smem_u32(sB + stage * B_STAGE_BYTES);
+          const uint32_t b_base = ptx::smem_u32(resident ? sB + kb * (bn * GEMM_BK * 2) : sB + stage * B_STAGE_BYTES);
 #pragma unroll
           for (int k = 0; k < GEMM_BK / 16; ++k) {
             ptx::umma_ss(d_tmem, ptx::make_sw128_kmajor_desc(a_base + k * 32), ptx::make_sw128_kmajor_desc(b_base + k * 32),
@@ -145,16 +167,15 @@ tapgemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
       }
     }
   } else {
-    // ------------------------------------------------------------------ epilogue (warps 2..5)
+    // ------------------------------------------------------------------ epilogue (warps 2..9)
     const int lane_grp = warp & 3;               // TMEM lanes [32*lane_grp, +32) are accessible to this warp
+    const int half = (warp - 2) >> 2;            // which of the interleaved column chunks this warp takes
     const int row = lane_grp * 32 + lane;
     int acc = 0;
     uint32_t acc_ph = 0;
-    for (int item = blockIdx.x; item < total; item += gridDim.x) {
-      const int nt = item % n_tiles;
-      const int rest = item / n_tiles;
-      const int phase = rest % p.n_phase;
-      const int mt = rest / p.n_phase;
+    for (int it = it0; it < it_end; it += it_step) {
+      int mt, phase, nt;
+      decode(it, mt, phase, nt);
       const int b = __ldg(p.tile_seq + mt);
       const int lrow = __ldg(p.tile_row0 + mt) + row;
       const int slen = __ldg(p.seq_len + b);
@@ -165,8 +186,8 @@ tapgemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
       ptx::mbar_wait(&tfull[acc], acc_ph);
       ptx::tc_fence_after();
       const uint32_t taddr = tmem_base + ((uint32_t)(lane_grp * 32) << 16) + acc * 256;
-      if ((bn & 31) == 0) epilogue_chunks<32>(p, taddr, bn, nt * bn, (size_t)m, b, valid, phase, lane);
-      else epilogue_chunks<16>(p, taddr, bn, nt * bn, (size_t)m, b, valid, phase, lane);
+      if ((bn & 31) == 0) epilogue_chunks<32>(p, taddr, bn, nt * bn, (size_t)m, b, valid, phase, lane, half);
+      else epilogue_chunks<16>(p, taddr, bn, nt * bn, (size_t)m, b, valid, phase, lane, half);
       ptx::tc_fence_before();
       ptx::mbar_arrive(&tempty[acc]);
       acc ^= 1;
@@ -250,9 +271,20 @@ int launch_tapgemm_tc(const GemmParams& p, cudaStream_t stream) {
   CVB_TRY(make_map_2d(&tmA, p.A, (uint64_t)p.a_cols, (uint64_t)p.a_rows, (uint64_t)p.lda, GEMM_BK, TILE_M));
   const uint64_t K = (uint64_t)p.n_seg * p.seg_len;
   CVB_TRY(make_map_2d(&tmW, p.W, K, (uint64_t)p.n_phase * p.n_pad, K, GEMM_BK, (uint32_t)p.bn));
-  const int total = p.m_tiles * p.n_phase * (p.n_pad / p.bn);
-  const int grid = total < num_sms() ? total : num_sms();
-  tapgemm_tc_kernel<<<grid, NUM_THREADS, SMEM_BYTES, stream>>>(tmA, tmW, p);
+  const int keys = p.n_phase * (p.n_pad / p.bn);
+  const int total = p.m_tiles * keys;
+  const int sms = num_sms();
+  const bool resident = (uint64_t)p.bn * K * 2 <= (uint64_t)STAGES * B_STAGE_BYTES && keys <= sms &&
+                        (p.bn * GEMM_BK * 2) % 1024 == 0;
+  int grid;
+  if (resident) {
+    int per_key = sms / keys;
+    if (per_key > p.m_tiles) per_key = p.m_tiles;
+    grid = per_key * keys;
+  } else {
+    grid = total < sms ? total : sms;
+  }
+  tapgemm_tc_kernel<<<grid, NUM_THREADS, SMEM_BYTES, stream>>>(tmA, tmW, p, resident ? 1 : 0);
   CVB_LAUNCH_CHECK();
   return CVB_OK;
 }
