@@ -23,7 +23,7 @@ constexpr int A_STAGE_BYTES = TILE_M * GEMM_BK * 2;        // 16 KiB
 constexpr int B_STAGE_BYTES = 256 * GEMM_BK * 2;           // 32 KiB (bn <= 256)
 constexpr int BAR_BYTES = 256;
 constexpr int SMEM_BYTES = 1024 + STAGES * (A_STAGE_BYTES + B_STAGE_BYTES) + BAR_BYTES;
-constexpr int EPI_WARPS = 8;                                 // 2 per TMEM lane group: chunks interleaved between them
+constexpr int EPI_WARPS = 16;                                // 2 per TMEM lane group: chunks interleaved between them
 constexpr int NUM_THREADS = 64 + 32 * EPI_WARPS;
 constexpr int TMEM_COLS = 512;
 
