@@ -11,8 +11,9 @@
 //                   S[128x128] = Q K^T        (SS, both operands K-major)
 //                   O[128x64] += P V          (A = P from TMEM as packed bf16, B = V tile read MN-major in place:
 //                                              no transposed copy of V is ever made)
-//   warps 2..5  : softmax, one query row per thread (TMEM lane): tcgen05.ld S, running max / sum in registers,
-//                 exp2, pack to bf16, tcgen05.st P; O is rescaled in TMEM only when some row max of the warp moved.
+//   warps 2..9  : softmax, two threads per query row (64 scores each, kept in registers): tcgen05.ld S, max
+//                 (halves exchanged through smem), exp2, pack to bf16, tcgen05.st P; O is rescaled in TMEM only
+//                 when some row max of the warp moved.
 // TMEM columns: S [0,128) fp32, P [128,192) packed bf16, O [192,256) fp32.
 #include <cuda.h>
 #include <mutex>
@@ -29,7 +30,7 @@ namespace {
 constexpr int HD = 64, BQ = 128, BK = 128;
 constexpr int TILE_BYTES = 128 * 64 * 2;            // 16 KiB
 constexpr int KV_STAGES = 2;
-constexpr int SMEM_BYTES = 1024 + TILE_BYTES * (1 + 2 * KV_STAGES) + 128;
+constexpr int SMEM_BYTES = 1024 + TILE_BYTES * (1 + 2 * KV_STAGES) + 128 + 2 * 2 * 128 * 4;
 constexpr int TM_S = 0, TM_P = 128, TM_O = 192, TM_COLS = 256;
 
 // MN-major 128B-swizzled shared-memory operand (V tile: rows = keys (K dim), 64 d (N dim) contiguous = 128 B).
@@ -55,7 +56,7 @@ __device__ __forceinline__ uint32_t pack2(float lo, float hi) {
   return *reinterpret_cast<uint32_t*>(&t);
 }
 
-__global__ void __launch_bounds__(192, 2)
+__global__ void __launch_bounds__(320, 2)
 attention_tc_kernel(const __grid_constant__ CUtensorMap tm, __nv_bfloat16* __restrict__ out, int ldo, const Layout lay,
                     int heads, float scale_log2) {
   const int head = blockIdx.x % heads, tile = blockIdx.x / heads;
@@ -81,14 +82,15 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tm, __nv_bfloat16* __res
   uint64_t* p_full = bars + 7;
   uint64_t* pv_done = bars + 8;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 9);
+  float* smax = reinterpret_cast<float*>(bars + 10);      // [2 parities][2 halves][128 rows]
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   if (threadIdx.x == 0) {
     ptx::mbar_init(q_full, 1);
     for (int i = 0; i < KV_STAGES; ++i) { ptx::mbar_init(&kv_full[i], 1); ptx::mbar_init(&kv_empty[i], 1); }
     ptx::mbar_init(s_full, 1);
-    ptx::mbar_init(s_free, 128);
-    ptx::mbar_init(p_full, 128);
+    ptx::mbar_init(s_free, 256);
+    ptx::mbar_init(p_full, 256);
     ptx::mbar_init(pv_done, 1);
     ptx::fence_barrier_init();
     ptx::prefetch_tensormap(&tm);
@@ -144,103 +146,98 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tm, __nv_bfloat16* __res
       }
     }
   } else {
-    // ------------------------------------------------------------------ softmax + output (warps 2..5)
+    // ------------------------------------------------------------------ softmax + output (warps 2..9)
+    // Two warps per TMEM lane group: thread (row, half) owns 64 of the row's 128 scores, which stay in
+    // registers between the max and the exp pass (one batch of tcgen05.ld per block); the two halves of a
+    // row exchange their maxima through shared memory.
     const int lane_grp = warp & 3;
+    const int half = (warp - 2) >> 2;
     const int row = lane_grp * 32 + lane;
     const uint32_t tbase = tmem + ((uint32_t)(lane_grp * 32) << 16);
-    float m_run = -INFINITY, l_run = 0.f;
+    float m_run = -INFINITY, l_half = 0.f;
     for (int j = 0; j < nblk; ++j) {
       ptx::mbar_wait(s_full, j & 1);
       ptx::tc_fence_after();
-      const int nvalid = len - j * BK;                        // keys of this block inside the sequence
-      // pass 1: row max
-      float mx4[4] = {m_run, m_run, m_run, m_run};                   // independent chains: no 128-long dependency
+      const int nvalid = len - j * BK - half * 64;            // valid keys among this thread's 64 columns
+      uint32_t raw[2][32];
+      ptx::tmem_ld32_nowait(tbase + TM_S + half * 64, raw[0]);
+      ptx::tmem_ld32_nowait(tbase + TM_S + half * 64 + 32, raw[1]);
+      ptx::tmem_wait_ld();
+      ptx::tc_fence_before();
+      ptx::mbar_arrive(s_free);                               // S(j) is in registers: QK(j+1) may overwrite it
+      float v[64];
 #pragma unroll
-      for (int c = 0; c < BK; c += 32) {
-        float v[32];
-        ptx::tmem_ld32(tbase + TM_S + c, v);
-        if (nvalid < BK) {
+      for (int i = 0; i < 64; ++i) v[i] = __uint_as_float(raw[i >> 5][i & 31]);
+      if (nvalid < 64) {
 #pragma unroll
-          for (int i = 0; i < 32; ++i) if (c + i >= nvalid) v[i] = -INFINITY;
-        }
-#pragma unroll
-        for (int i = 0; i < 32; i += 4) {
-          mx4[0] = fmaxf(mx4[0], v[i]);
-          mx4[1] = fmaxf(mx4[1], v[i + 1]);
-          mx4[2] = fmaxf(mx4[2], v[i + 2]);
-          mx4[3] = fmaxf(mx4[3], v[i + 3]);
-        }
+        for (int i = 0; i < 64; ++i) if (i >= nvalid) v[i] = -INFINITY;
       }
-      const float m_new = fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3]));
+      float mx4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
+#pragma unroll
+      for (int i = 0; i < 64; i += 4) {
+        mx4[0] = fmaxf(mx4[0], v[i]);
+        mx4[1] = fmaxf(mx4[1], v[i + 1]);
+        mx4[2] = fmaxf(mx4[2], v[i + 2]);
+        mx4[3] = fmaxf(mx4[3], v[i + 3]);
+      }
+      const float m_loc = fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3]));
+      float* xch = smax + (j & 1) * 256;
+      xch[half * 128 + row] = m_loc;
+      ptx::named_bar_sync(1, 256);
+      const float m_new = fmaxf(m_run, fmaxf(m_loc, xch[(half ^ 1) * 128 + row]));
       const float corr = ex2_approx((m_run - m_new) * scale_log2);   // first block: exp2(-inf) = 0
       const bool moved = __any_sync(0xffffffffu, m_new > m_run);
       m_run = m_new;
       const float moff = m_new * scale_log2;
       if (j > 0) ptx::mbar_wait(pv_done, (j - 1) & 1);               // PV(j-1) retired: P and O may be touched
       ptx::tc_fence_after();
-      // pass 2: p = exp2(s*scale - m*scale), packed to bf16 into the P columns
       float ls4[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
-      for (int c = 0; c < BK; c += 32) {
-        float v[32];
-        ptx::tmem_ld32(tbase + TM_S + c, v);
+      for (int c = 0; c < 64; c += 32) {
         uint32_t pk[16];
 #pragma unroll
         for (int i = 0; i < 32; i += 2) {
-          float p0 = ex2_approx(fmaf(v[i], scale_log2, -moff));
-          float p1 = ex2_approx(fmaf(v[i + 1], scale_log2, -moff));
-          if (nvalid < BK) {
-            if (c + i >= nvalid) p0 = 0.f;
-            if (c + i + 1 >= nvalid) p1 = 0.f;
-          }
+          const float p0 = ex2_approx(fmaf(v[c + i], scale_log2, -moff));       // masked columns: exp2(-inf) = 0
+          const float p1 = ex2_approx(fmaf(v[c + i + 1], scale_log2, -moff));
           ls4[(i >> 1) & 3] += p0 + p1;
           pk[i >> 1] = pack2(p0, p1);
         }
-        ptx::tmem_st16(tbase + TM_P + (c >> 1), pk);
+        ptx::tmem_st16(tbase + TM_P + half * 32 + (c >> 1), pk);
       }
-      const float lsum = (ls4[0] + ls4[1]) + (ls4[2] + ls4[3]);
-      ptx::tc_fence_before();
-      ptx::mbar_arrive(s_free);                                      // S(j) fully consumed
-      l_run = l_run * corr + lsum;
-      if (j > 0 && moved) {                                          // rescale the running output
+      l_half = l_half * corr + ((ls4[0] + ls4[1]) + (ls4[2] + ls4[3]));
+      if (j > 0 && moved) {                                          // rescale this thread's 32 output columns
+        float o[32];
+        ptx::tmem_ld32(tbase + TM_O + half * 32, o);
+        uint32_t lo[16], hi[16];
 #pragma unroll
-        for (int c = 0; c < HD; c += 32) {
-          float o[32];
-          ptx::tmem_ld32(tbase + TM_O + c, o);
-          uint32_t w[32];
-#pragma unroll
-          for (int i = 0; i < 32; ++i) w[i] = __float_as_uint(o[i] * corr);
-          uint32_t lo[16], hi[16];
-#pragma unroll
-          for (int i = 0; i < 16; ++i) { lo[i] = w[i]; hi[i] = w[16 + i]; }
-          ptx::tmem_st16(tbase + TM_O + c, lo);
-          ptx::tmem_st16(tbase + TM_O + c + 16, hi);
-        }
+        for (int i = 0; i < 16; ++i) { lo[i] = __float_as_uint(o[i] * corr); hi[i] = __float_as_uint(o[16 + i] * corr); }
+        ptx::tmem_st16(tbase + TM_O + half * 32, lo);
+        ptx::tmem_st16(tbase + TM_O + half * 32 + 16, hi);
       }
       ptx::tmem_wait_st();
       ptx::tc_fence_before();
       ptx::mbar_arrive(p_full);
     }
-    // ---- epilogue: O / l -> bf16
+    // ---- epilogue: O / l -> bf16 (each thread writes 32 of the row's 64 output columns)
+    float* xch = smax + (nblk & 1) * 256;
+    xch[half * 128 + row] = l_half;
+    ptx::named_bar_sync(1, 256);
+    const float inv = 1.f / (l_half + xch[(half ^ 1) * 128 + row]);
     ptx::mbar_wait(pv_done, (nblk - 1) & 1);
     ptx::tc_fence_after();
-    const float inv = 1.f / l_run;
     const int lrow = q0 + row;
-    __nv_bfloat16* dst = out + (size_t)(seq0 + lrow) * ldo + head * HD;
+    float o[32];
+    ptx::tmem_ld32(tbase + TM_O + half * 32, o);
+    if (lrow < len) {
+      __nv_bfloat16* dst = out + (size_t)(seq0 + lrow) * ldo + head * HD + half * 32;
 #pragma unroll
-    for (int c = 0; c < HD; c += 32) {
-      float o[32];
-      ptx::tmem_ld32(tbase + TM_O + c, o);
-      if (lrow < len) {
-#pragma unroll
-        for (int i = 0; i < 32; i += 8) {
-          uint4 pk;
-          pk.x = pack2(o[i] * inv, o[i + 1] * inv);
-          pk.y = pack2(o[i + 2] * inv, o[i + 3] * inv);
-          pk.z = pack2(o[i + 4] * inv, o[i + 5] * inv);
-          pk.w = pack2(o[i + 6] * inv, o[i + 7] * inv);
-          *reinterpret_cast<uint4*>(dst + c + i) = pk;
-        }
+      for (int i = 0; i < 32; i += 8) {
+        uint4 pk;
+        pk.x = pack2(o[i] * inv, o[i + 1] * inv);
+        pk.y = pack2(o[i + 2] * inv, o[i + 3] * inv);
+        pk.z = pack2(o[i + 4] * inv, o[i + 5] * inv);
+        pk.w = pack2(o[i + 6] * inv, o[i + 7] * inv);
+        *reinterpret_cast<uint4*>(dst + i) = pk;
       }
     }
   }
@@ -295,7 +292,7 @@ int launch_attention_tc(const void* qkv, int ld, void* out, int ldo, const Layou
   });
   CVB_CUDA(attr_err);
   const int grid = (lay.rows / 128) * heads;
-  attention_tc_kernel<<<grid, 192, SMEM_BYTES, st>>>(tm, reinterpret_cast<__nv_bfloat16*>(out), ldo, lay, heads,
+  attention_tc_kernel<<<grid, 320, SMEM_BYTES, st>>>(tm, reinterpret_cast<__nv_bfloat16*>(out), ldo, lay, heads,
                                                      scale * 1.4426950408889634f);
   CVB_LAUNCH_CHECK();
   return CVB_OK;
