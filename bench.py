@@ -254,7 +254,7 @@ def run_ours(args):
                      "peak_source": pk["src"] + " bf16_tflops_sustained", "traffic": None,
                      "launches_per_step": tc["launches"], "kernel_ms_per_step": tc["ms"],
                      "share_of_eager_step": tc["ms"] / prof["_step_ms_eager"],
-                     "attention": {"kernel": "attention_bf16_kernel (mma.sync flash)", "launches": att["launches"],
+                     "attention": {"kernel": "attention_tc_kernel (tcgen05/TMEM flash)", "launches": att["launches"],
                                    "ms": att["ms"], "achieved_tflops": att["flops"] / (att["ms"] * 1e-3) / 1e12,
                                    "share_of_eager_step": att["ms"] / prof["_step_ms_eager"]}},
     }
