@@ -167,7 +167,7 @@ class B200BigVGAN:
         key = tuple(int(l) for l in lens)
         if key not in self._programs:
             if len(self._programs) >= 4:
-                self._programs.pop(next(iter(self._programs)))
+                self._programs.pop(next(iter(self._programs))).__dict__.clear()
             self._programs[key] = _Program(self, key)
         return self._programs[key]
 

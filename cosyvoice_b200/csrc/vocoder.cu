@@ -4,8 +4,7 @@
 //   stft16 / istft16  16-point (i)STFT, hop 4, Hann             hifigan/generator.py:333-347,376-381
 //   snake             x + sin^2(a x)/(a + 1e-9)                 transformer/activation.py:79-82
 //   reflect_row0      ReflectionPad1d((1,0)) fix-up             hifigan/generator.py:358-359
-//   anti_alias_act    2x Kaiser-sinc up, SnakeBeta, 2x down     BigVGAN/alias_free_activation/torch/act.py:26-31
-//                     (= the reference's only native kernel, cuda/anti_alias_activation_cuda.cu:44-181)
+//   (the anti-aliased SnakeBeta activation lives in antialias.cu)
 #include "common.cuh"
 #include "../../include/cvb200.h"
 
@@ -229,131 +228,6 @@ __global__ void reflect_row0_kernel(void* __restrict__ x, int ldx, int dt, int C
     st_from_float(x, r0 * ldx + c, dt, ld_as_float(x, (r0 + 2) * ldx + c, dt));
 }
 
-// ------------------------------------------------------------------ anti-aliased SnakeBeta
-// up[2a]   = 2 * sum_{m<6} f[1+2m] * x[a+2-m],   up[2a+1] = 2 * sum_{m<6} f[2m] * x[a+3-m]   (x replicate-clamped)
-// z = up + sin^2(up * e^alpha) / (e^beta + 1e-9)
-// y[t]     = sum_{j<12} f[j] * z[clamp(2t + j - 5, 0, 2T-1)]
-constexpr int AA_TS = 64;                // output rows per CTA
-constexpr int AA_CH = 64;                // channels per CTA
-constexpr int AA_XR = AA_TS + 12;        // x rows staged: t0-6 .. t0+TS+5
-constexpr int AA_ZR = 2 * AA_TS + 12;    // z rows staged: 2 t0 - 5 .. 2 t0 + 2 TS + 6
-
-__global__ void __launch_bounds__(256) anti_alias_rows_kernel(const void* __restrict__ x, int ldx, int x_dt,
-                                                              void* __restrict__ out, int ldo, int out_dt,
-                                                              const float* __restrict__ filt, const float* __restrict__ alpha,
-                                                              const float* __restrict__ beta, int C, const Layout lay) {
-  extern __shared__ float aa_smem[];
-  float* sx = aa_smem;                    // [AA_XR][AA_CH]
-  float* sz = aa_smem + AA_XR * AA_CH;    // [AA_ZR][AA_CH]
-  __shared__ float f[12];
-  if (threadIdx.x < 12) f[threadIdx.x] = __ldg(filt + threadIdx.x);
-  const int row0 = blockIdx.x * AA_TS, c0 = blockIdx.y * AA_CH;
-  int b, t0, T;
-  row_info(lay, row0, b, t0, T);
-  const int c = threadIdx.x & (AA_CH - 1), tl = threadIdx.x >> 6;     // 4 time lanes
-  const int ch = c0 + c;
-  const bool ch_ok = ch < C;
-  if (t0 >= T) {                          // padding-only strip: keep it zero
-    if (ch_ok)
-      for (int j = tl; j < AA_TS; j += 4) st_from_float(out, (size_t)(row0 + j) * ldo + ch, out_dt, 0.f);
-    return;
-  }
-  const size_t seq_base = (size_t)(row0 - t0);       // global row of the sequence's frame 0
-  for (int j = tl; j < AA_XR; j += 4) {
-    int t = t0 - 6 + j;
-    t = min(max(t, 0), T - 1);
-    sx[j * AA_CH + c] = ch_ok ? ld_as_float(x, (seq_base + t) * ldx + ch, x_dt) : 0.f;
-  }
-  __syncthreads();
-  const float ea = ch_ok ? expf(__ldg(alpha + ch)) : 1.f;
-  const float ib = ch_ok ? 1.f / (expf(__ldg(beta + ch)) + 1e-9f) : 0.f;
-  for (int j = tl; j < AA_ZR; j += 4) {
-    int u = 2 * t0 - 5 + j;
-    u = min(max(u, 0), 2 * T - 1);
-    const int a = u >> 1;
-    // x index a + 2 - m (even u) / a + 3 - m (odd u), m = 0..5; staged row of x index i is i - (t0 - 6).
-    // x indices outside [0, T) must be clamped: staged rows were filled with clamped values for
-    // t in [t0-6, t0+TS+5], and a+3 <= t0+TS+5+? holds because u <= 2 t0 + 2 TS + 6 -> a <= t0 + TS + 3.
-    const int base = a + ((u & 1) ? 3 : 2) - (t0 - 6);
-    float acc = 0.f;
-#pragma unroll
-    for (int m = 0; m < 6; ++m) {
-      int r = base - m;
-      r = min(max(r, 0), AA_XR - 1);
-      acc = fmaf(f[(u & 1) ? 2 * m : 2 * m + 1], sx[r * AA_CH + c], acc);
-    }
-    const float up = 2.f * acc;
-    const float sv = sinf(up * ea);
-    sz[j * AA_CH + c] = up + sv * sv * ib;
-  }
-  __syncthreads();
-  for (int j = tl; j < AA_TS; j += 4) {
-    const int t = t0 + j;
-    float y = 0.f;
-    if (t < T) {
-      // z index 2t + q - 5 (clamped) -> staged row (clamped index) - (2 t0 - 5)
-#pragma unroll
-      for (int q = 0; q < 12; ++q) {
-        int u = 2 * t + q - 5;
-        u = min(max(u, 0), 2 * T - 1);
-        y = fmaf(f[q], sz[(u - (2 * t0 - 5)) * AA_CH + c], y);
-      }
-    }
-    if (ch_ok) st_from_float(out, (size_t)(row0 + j) * ldo + ch, out_dt, y);
-  }
-}
-
-// [B, C, T] contiguous variant: drop-in for the reference's fwd_cuda.  One CTA per (256-sample strip, row b*C+c).
-constexpr int NC_TS = 256;
-__global__ void __launch_bounds__(256) anti_alias_nct_kernel(const void* __restrict__ x, void* __restrict__ y, int dt, int C,
-                                                             int T, const float* __restrict__ fu,
-                                                             const float* __restrict__ fd, const float* __restrict__ alpha,
-                                                             const float* __restrict__ beta) {
-  __shared__ float sx[NC_TS + 12];
-  __shared__ float sz[2 * NC_TS + 12];
-  __shared__ float su[12], sd[12];
-  if (threadIdx.x < 12) {
-    su[threadIdx.x] = __ldg(fu + threadIdx.x);
-    sd[threadIdx.x] = __ldg(fd + threadIdx.x);
-  }
-  const int t0 = blockIdx.x * NC_TS;
-  const size_t rowbase = (size_t)blockIdx.y * T;
-  const int ch = blockIdx.y % C;
-  for (int j = threadIdx.x; j < NC_TS + 12; j += 256) {
-    const int t = min(max(t0 - 6 + j, 0), T - 1);
-    sx[j] = ld_as_float(x, rowbase + t, dt);
-  }
-  __syncthreads();
-  const float ea = expf(__ldg(alpha + ch));
-  const float ib = 1.f / (expf(__ldg(beta + ch)) + 1e-9f);
-  for (int j = threadIdx.x; j < 2 * NC_TS + 12; j += 256) {
-    int u = 2 * t0 - 5 + j;
-    u = min(max(u, 0), 2 * T - 1);
-    const int a = u >> 1;
-    const int base = a + ((u & 1) ? 3 : 2) - (t0 - 6);
-    float acc = 0.f;
-#pragma unroll
-    for (int m = 0; m < 6; ++m) {
-      const int r = min(max(base - m, 0), NC_TS + 11);
-      acc = fmaf(su[(u & 1) ? 2 * m : 2 * m + 1], sx[r], acc);
-    }
-    const float up = 2.f * acc;
-    const float sv = sinf(up * ea);
-    sz[j] = up + sv * sv * ib;
-  }
-  __syncthreads();
-  const int t = t0 + threadIdx.x;
-  if (t < T) {
-    float o = 0.f;
-#pragma unroll
-    for (int q = 0; q < 12; ++q) {
-      const int u = min(max(2 * t + q - 5, 0), 2 * T - 1);
-      o = fmaf(sd[q], sz[u - (2 * t0 - 5)], o);
-    }
-    st_from_float(y, rowbase + t, dt, o);
-  }
-}
-
 }  // namespace
 
 // ------------------------------------------------------------------ launchers
@@ -409,31 +283,6 @@ int launch_snake(const void* x, int ldx, int x_dt, void* out, int ldo, int out_d
 int launch_reflect_row0(void* x, int ldx, int dt, int C, const Layout& lay, cudaStream_t st) {
   if (lay.n_seq <= 0) return CVB_OK;
   reflect_row0_kernel<<<lay.n_seq, 128, 0, st>>>(x, ldx, dt, C, lay);
-  CVB_LAUNCH_CHECK();
-  return CVB_OK;
-}
-
-int launch_anti_alias_rows(const void* x, int ldx, int x_dt, void* out, int ldo, int out_dt, const float* filt,
-                           const float* alpha, const float* beta, int C, const Layout& lay, cudaStream_t st) {
-  if (lay.rows <= 0) return CVB_OK;
-  constexpr int SMEM = (AA_XR + AA_ZR) * AA_CH * (int)sizeof(float);
-  static bool attr_done = false;
-  if (!attr_done) {
-    CVB_CUDA(cudaFuncSetAttribute(anti_alias_rows_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM));
-    attr_done = true;
-  }
-  dim3 grid(lay.rows / AA_TS, ceil_div(C, AA_CH));
-  anti_alias_rows_kernel<<<grid, 256, SMEM, st>>>(x, ldx, x_dt, out, ldo, out_dt, filt, alpha, beta, C, lay);
-  CVB_LAUNCH_CHECK();
-  return CVB_OK;
-}
-
-int launch_anti_alias_nct(const void* x, void* y, int dt, int B, int C, int T, const float* fu, const float* fd,
-                          const float* alpha, const float* beta, cudaStream_t st) {
-  if (B <= 0 || C <= 0 || T <= 0) return CVB_OK;      // the reference kernel is a silent no-op on seq_len == 0 (.cu:195-198)
-  CVB_REQUIRE((long long)B * C <= 65535, "B*C exceeds grid.y");
-  dim3 grid(ceil_div(T, NC_TS), B * C);
-  anti_alias_nct_kernel<<<grid, 256, 0, st>>>(x, y, dt, C, T, fu, fd, alpha, beta);
   CVB_LAUNCH_CHECK();
   return CVB_OK;
 }

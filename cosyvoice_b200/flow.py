@@ -144,6 +144,7 @@ class _Program:
             lays.append(lays[-1].derive(1, 2, [(l + 1) // 2 for l in lays[-1].lens]))
         cats = [z(lays[i].rows, 2 * C) for i in range(n_down)]      # [h | skip] inputs of the up path
         self.cats = cats
+        self.lays = lays
 
         cur_in, cur_lay = self.A0, lay
         # ---- down path (flow/decoder.py:254-279)
@@ -186,6 +187,17 @@ class _Program:
         self._gemm(fb["conv"], self.fin, lay, self.h, gn_stats=stats)
         self.ops.append(ops.norm_mish_op(self.h, self.hn, fb["gamma"], fb["beta"], lay, gn_stats=stats))
         self._gemm(w.final_proj, self.hn, lay, self.v)
+
+    def release(self):
+        """Drop buffers and launch closures (reference cycles would otherwise keep the HBM until a gc pass)."""
+        self.__dict__.clear()
+
+    def set_lens(self, lens: Sequence[int]):
+        """Re-bind the program (and any CUDA graph captured over it) to other valid lengths under the same strides:
+        every kernel reads the lengths from the layouts' device arrays and re-zeroes the pad rows it owns."""
+        for i, L in enumerate(self.lays):
+            L.set_lens(lens, halo=max(1, 8 >> i))       # a level-i stride is stride0 / 2^i: the zero halo shrinks with it
+            lens = [(l + 1) // 2 for l in lens]
 
     # -- helpers
     def _next_stats(self):
@@ -278,13 +290,17 @@ class B200Estimator:
         return SeqLayout.build(lens, self.device, align=align, halo=8)
 
     def program(self, lay: SeqLayout) -> _Program:
-        key = lay.key()
+        """Programs are cached per STRIDE pattern (lengths are device data, re-bound in place), so a streaming
+        session whose T grows chunk by chunk reuses one program / CUDA graph per 128-row bucket."""
+        key = lay.stride_key()
         p = self._programs.get(key)
         if p is None:
-            if len(self._programs) >= 8:
-                self._programs.pop(next(iter(self._programs)))
-            p = _Program(self.weights, lay, self.engine)
+            if len(self._programs) >= 32:
+                self._programs.pop(next(iter(self._programs))).release()
+            p = _Program(self.weights, SeqLayout(lay.lens, lay.strides, self.device), self.engine)
             self._programs[key] = p
+        else:
+            p.set_lens(lay.lens)
         return p
 
     @torch.inference_mode()
@@ -362,8 +378,9 @@ class B200ConditionalCFM:
         prog = self.estimator.program(lay2)
         if not hasattr(prog, "cfm_state"):
             z = lambda: torch.zeros(lay1.rows, N_FEATS, dtype=torch.float32, device=self.device)
-            prog.cfm_state = dict(lay1=lay1, x=z(), mu=z(), cond=z(),
+            prog.cfm_state = dict(lay1=SeqLayout(lay1.lens, lay1.strides, self.device), x=z(), mu=z(), cond=z(),
                                   spks=torch.zeros(lay1.n_seq, N_FEATS, dtype=torch.float32, device=self.device))
+        prog.cfm_state["lay1"].set_lens(lay1.lens)
         return prog, prog.cfm_state
 
     def _steps(self, prog: _Program, st: dict, ts: List[float], dts: List[float]):
@@ -384,8 +401,10 @@ class B200ConditionalCFM:
         if not self.use_cuda_graph:
             self._steps(prog, st, ts, dts)
             return
-        key = (lay1.key(), n_timesteps)
+        key = (lay1.stride_key(), n_timesteps)
         g = self._graphs.get(key)
+        if g is not None and g[1] is not prog:      # the program of this bucket was evicted and rebuilt
+            g = None
         if g is None:
             # warm-up run on a side stream (also sets the kernels' function attributes), then capture
             keep = st["x"].clone()
@@ -401,8 +420,9 @@ class B200ConditionalCFM:
                 self._steps(prog, st, ts, dts)
             n_launch = _lib.launch_count() - n0
             st["x"].copy_(keep)
-            if len(self._graphs) >= 8:
+            if len(self._graphs) >= 32:
                 self._graphs.pop(next(iter(self._graphs)))
+            self._graphs = {k: v for k, v in self._graphs.items() if v[1].__dict__}     # drop graphs of released programs
             g = (graph, prog, n_launch)
             self._graphs[key] = g
         self.last_graph_launches = g[2]

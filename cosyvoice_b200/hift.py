@@ -87,13 +87,15 @@ class _Weights:
 class _Program:
     """Launch list + buffers of one batched HiFT forward over a fixed set of mel lengths."""
 
-    def __init__(self, w: _Weights, lens: Sequence[int], engine: int):
+    def __init__(self, w: _Weights, lens: Sequence[int], engine: int, strides: Optional[Sequence[int]] = None):
         self.w, self.engine = w, engine
         dev, dt = w.device, w.dtype
         self.lens = [int(l) for l in lens]
         B = len(self.lens)
-        lay0 = SeqLayout.build(self.lens, dev, align=128, halo=8)
+        lay0 = (SeqLayout.build(self.lens, dev, align=128, halo=8) if strides is None
+                else SeqLayout(self.lens, strides, dev))
         self.lay0 = lay0
+        self.Lm = None
         z = lambda *shape, dtype=dt: torch.zeros(*shape, dtype=dtype, device=dev)
         f32 = torch.float32
         R0 = lay0.rows
@@ -107,7 +109,10 @@ class _Program:
             self.lays.append(lay0.derive(P, 1, [l * P + extra for l in self.lens]))
         self.P = P
         lay_f = self.lays[-1]
-        self.l_max = max(self.lens) * w.hop
+        # sample buffers are sized for the longest utterance the strides admit, so that the program can be re-bound
+        # to other lengths of the same stride bucket (set_lens); l_cur = samples of the longest CURRENT utterance
+        self.l_max = (max(lay0.strides) - 8) * w.hop
+        self.l_cur = max(self.lens) * w.hop
         assert self.l_max % 4 == 0
         # ---- inputs / source path
         self.mel32 = z(R0, 128, dtype=f32)
@@ -155,6 +160,7 @@ class _Program:
             # ups[i] (+ ReflectionPad1d((1,0)) on the last stage): M space = input rows
             if last:
                 Lm = lay_prev.with_lens([l + 1 for l in lay_prev.lens])
+                self.Lm, self._Lm_P = Lm, P // w.rates[-1]
                 self._gemm(w.ups[i], x_prev, Lm, xm, out_limit=L.seq_len, flop_lens=lay_prev.lens)
                 self.ops.append(lambda xm=xm, Cc=Cc, L=L: ops.reflect_row0(xm, Cc, L))
             else:
@@ -180,6 +186,27 @@ class _Program:
         self._gemm(w.conv_post, x_prev, lay_f, self.cp)
         self.marks["conv_post"] = (len(self.ops), self.cp, lay_f)
         self.ops.append(lambda: ops.istft16(self.cp, lay_f, self.wav, 0.99))
+
+    def release(self):
+        """Drop buffers and launch closures (they reference each other in cycles: without this an evicted program
+        keeps its HBM until the next Python gc pass)."""
+        self.__dict__.clear()
+
+    def set_lens(self, lens: Sequence[int]):
+        """Re-bind to other mel lengths under the same strides (every kernel reads lengths from device arrays and
+        re-zeroes the pad rows it owns)."""
+        lens = [int(l) for l in lens]
+        if lens == self.lens:
+            return
+        self.lay0.set_lens(lens)
+        n_up, P = len(self.lays), 1
+        for i, u in enumerate(self.w.rates):
+            P *= u
+            self.lays[i].set_lens([l * P + (1 if i == n_up - 1 else 0) for l in lens])
+        if self.Lm is not None:
+            self.Lm.set_lens([l * self._Lm_P + 1 for l in lens], halo=0)
+        self.lens = lens
+        self.l_cur = max(lens) * self.w.hop
 
     def _gemm(self, plan, A, L, out0, flop_lens=None, **kw):
         fl = plan.flops_per_row * sum(flop_lens if flop_lens is not None else L.lens)
@@ -221,34 +248,43 @@ class B200HiFTGenerator:
         self.hop = self.weights.hop
         self._programs: Dict[tuple, _Program] = {}
 
-    def program(self, lens: Sequence[int]) -> _Program:
-        key = tuple(int(l) for l in lens)
+    def program(self, lens: Sequence[int], uniform_stride: bool = False) -> _Program:
+        """Programs are cached per stride pattern (128-frame buckets) and re-bound to the lengths of each call.
+        uniform_stride: every utterance gets the stride of the longest one, so that ragged batches of one length
+        bucket share a program (shard.make_batches)."""
+        lens = [int(l) for l in lens]
+        key = tuple((l + 8 + 127) // 128 * 128 for l in lens)
+        if uniform_stride:
+            key = (max(key),) * len(key)
         p = self._programs.get(key)
         if p is None:
-            if len(self._programs) >= 4:
-                self._programs.pop(next(iter(self._programs)))
-            p = _Program(self.weights, key, self.engine)
+            if len(self._programs) >= 8:
+                self._programs.pop(next(iter(self._programs))).release()
+            p = _Program(self.weights, lens, self.engine, strides=key)
             self._programs[key] = p
+        else:
+            p.set_lens(lens)
         return p
 
     def draw_source_rng(self, prog: _Program):
         """Same draws, shapes, devices and order as the reference (generator.py:149-150 CPU Uniform sample,
         :163 randn_like(sine_waves) and :219 randn_like(uv) on the model device)."""
-        B, L = len(prog.lens), prog.l_max
+        B, L = len(prog.lens), prog.l_cur
         u = Uniform(low=-np.pi, high=np.pi).sample(sample_shape=(B, NB_HARM + 1, 1))
         u[:, 0, :] = 0
         prog.phase.copy_(u.reshape(B, NB_HARM + 1))
-        prog.noise.copy_(torch.randn(B, NB_HARM + 1, L, device=self.device))
+        prog.noise[:, :, :L].copy_(torch.randn(B, NB_HARM + 1, L, device=self.device))
         torch.randn(B, L, 1, device=self.device)          # consumed and discarded by the reference (:219)
 
     @torch.inference_mode()
     def inference_batch(self, mels: Sequence[torch.Tensor], phase_vec: Optional[torch.Tensor] = None,
                         noise: Optional[torch.Tensor] = None, cache_sources: Optional[Sequence[torch.Tensor]] = None,
-                        source: Optional[torch.Tensor] = None) -> Tuple[List[torch.Tensor], List[torch.Tensor]]:
+                        source: Optional[torch.Tensor] = None, uniform_stride: bool = False
+                        ) -> Tuple[List[torch.Tensor], List[torch.Tensor]]:
         """mels: per-utterance [1,80,T_u].  phase_vec [B,9,1] / noise [B,9,L_max]: injected RNG (tests);
         source [B,1,L_max]: bypass the source module entirely.  Returns ([wav [1,L_u]], [s [1,1,L_u]])."""
         lens = [int(m.shape[-1]) for m in mels]
-        prog = self.program(lens)
+        prog = self.program(lens, uniform_stride)
         B, dev = len(lens), self.device
         T_max = max(lens)
         buf = torch.zeros(B, 80, T_max, dtype=torch.float32, device=dev)

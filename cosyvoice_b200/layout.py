@@ -62,6 +62,21 @@ class SeqLayout:
             strides.append(s * num // den)
         return SeqLayout(lens, strides, self.device)
 
+    def set_lens(self, lens: Sequence[int], halo: int = 8) -> None:
+        """Re-bind the valid lengths IN PLACE (strides, row offsets and every device pointer stay): a program or
+        CUDA graph built on this layout then serves any batch whose lengths fit the same strides.  The copy is
+        stream-ordered on the current stream."""
+        lens = [int(l) for l in lens]
+        assert len(lens) == self.n_seq
+        for l, s in zip(lens, self.strides):
+            assert 0 <= l and l + halo <= s, (l, s)
+        if lens == self.lens:
+            return
+        self.lens = lens
+        self.max_len = max(lens)
+        self.seq_len.copy_(torch.tensor(lens, dtype=torch.int32))
+        self._c = None
+
     def with_lens(self, lens: Sequence[int]) -> "SeqLayout":
         return SeqLayout(lens, self.strides, self.device)
 
@@ -78,3 +93,6 @@ class SeqLayout:
 
     def key(self):
         return (tuple(self.lens), tuple(self.strides))
+
+    def stride_key(self):
+        return tuple(self.strides)

@@ -28,7 +28,7 @@ class AcousticBackend:
         the prompt (flow/flow.py:144-158: they are generated and then dropped).  Returns waveforms [1, L_u] on device."""
         mels = self.cfm.solve_batch(mus, spks, conds, zs, n_timesteps)
         gen = [m[:, :, p:] for m, p in zip(mels, prompt_lens)]
-        wavs, _ = self.hift.inference_batch(gen)
+        wavs, _ = self.hift.inference_batch(gen, uniform_stride=True)
         return wavs
 
     # ---- device-resident variant used by bench.py's `value` leg ---------------------------------

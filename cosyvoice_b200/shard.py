@@ -43,19 +43,19 @@ def lpt_assign(costs: Sequence[float], n_ranks: int) -> List[List[int]]:
 
 def make_batches(indices: Sequence[int], lens: Sequence[int], row_budget: int = 48 * 1024, align: int = 256,
                  max_batch: int = 64) -> List[List[int]]:
-    """Group a rank's utterances (sorted by length so strides waste little) into batches whose packed row count
-    (sum of round_up(len + 8, align)) stays under `row_budget`."""
-    idx = sorted(indices, key=lambda i: (lens[i], i))
-    batches, cur, rows = [], [], 0
-    for i in idx:
-        r = (lens[i] + 8 + align - 1) // align * align
-        if cur and (rows + r > row_budget or len(cur) >= max_batch):
-            batches.append(cur)
-            cur, rows = [], 0
-        cur.append(i)
-        rows += r
-    if cur:
-        batches.append(cur)
+    """Group a rank's utterances into batches of ONE stride bucket each (stride = round_up(len + 8, align)), at most
+    row_budget // stride (and max_batch) utterances per batch.  Uniform strides mean every full batch of a bucket
+    has the same layout pattern, so the estimator program and its CUDA graph are built once per bucket and re-bound
+    to each batch's lengths (SeqLayout.set_lens); only the last, partial batch of a bucket needs a second one."""
+    buckets: Dict[int, List[int]] = {}
+    for i in sorted(indices, key=lambda i: (lens[i], i)):
+        stride = (lens[i] + 8 + align - 1) // align * align
+        buckets.setdefault(stride, []).append(i)
+    batches: List[List[int]] = []
+    for stride in sorted(buckets):
+        nb = max(1, min(max_batch, row_budget // stride))
+        idx = buckets[stride]
+        batches += [idx[k:k + nb] for k in range(0, len(idx), nb)]
     return batches
 
 

@@ -140,3 +140,26 @@ def test_varlen_batch_equals_per_utterance_oracle(graph):
         t_span = flow_ref.cosine_t_span(4)
         want = flow_ref.solve_euler(sd, zs[b], t_span, mus[b], torch.ones(1, 1, l), spks[b], conds[b])
         assert (mels[b].cpu() - want).abs().max().item() < 2e-3, (b, l)
+
+
+@pytest.mark.parametrize("causal", [False, True])
+def test_program_rebinds_lengths_under_one_stride_bucket(causal):
+    """Streaming reuse (BASELINE config 3): a program / CUDA graph captured at one length serves other lengths
+    that fit the same 128-row stride bucket (longer, then shorter: stale rows of the longer run must not leak).
+    Each result equals the oracle's own B=1 solve at that length."""
+    g = torch.Generator().manual_seed(21)
+    sd = init_weights.flow_estimator_sd(causal, seed=0)
+    cfm = (B200CausalConditionalCFM if causal else B200ConditionalCFM)(_estimator(causal, torch.float32))
+    cfm.use_cuda_graph = True
+    n_prog0 = None
+    for l in (60, 110, 37):
+        mu, z = torch.randn(1, 80, l, generator=g), torch.randn(1, 80, l, generator=g)
+        spk = torch.randn(1, 80, generator=g)
+        cond = torch.zeros(1, 80, l)
+        cond[:, :, :9] = torch.randn(1, 80, 9, generator=g) * 2 - 4
+        mel = cfm.solve_batch([mu], [spk], [cond], [z], 3)[0].cpu()
+        want = flow_ref.solve_euler(sd, z, flow_ref.cosine_t_span(3), mu, torch.ones(1, 1, l), spk, cond, causal=causal)
+        assert (mel - want).abs().max().item() < 2e-3, l
+        if n_prog0 is None:
+            n_prog0 = len(cfm._graphs)
+    assert len(cfm._graphs) == n_prog0        # one graph served all three lengths

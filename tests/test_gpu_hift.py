@@ -186,3 +186,24 @@ def test_bigvgan_trunk_matches_reference_golden(golden_dir):
     want1 = bigvgan_ref.trunk_forward(sd, feat[1:2, :, :5], d["spk"][1:2], d["topology"])
     assert (wav_r[1, :want1.shape[-1]] - want1[0]).abs().max().item() < 2e-4
     assert (wav_r[0] - d["wav"][0]).abs().max().item() < 2e-4
+
+
+@pytest.mark.parametrize("ver", ["v1", "v2"])
+def test_hift_program_rebinds_lengths(golden_dir, ver):
+    """Streaming reuse: one program per 128-frame stride bucket serves longer and then shorter mels; the stale rows
+    of the longer run must not leak into the shorter one (golden waveform of the real reference still matches)."""
+    d = _load(golden_dir, f"hift_{ver}.pt")
+    gen = _gen(d["v2"], torch.float32)
+    T = d["mel"].shape[-1]
+    g = torch.Generator().manual_seed(9)
+    long_mel = torch.randn(1, 80, T + 41, generator=g) * 2 - 4
+    long_src = torch.randn(1, 1, (T + 41) * gen.hop, generator=g) * 0.3
+    n0 = len(gen._programs)
+    gen.inference_batch([long_mel], source=long_src)
+    n1 = len(gen._programs)
+    wavs, _ = gen.inference_batch([d["mel"]], source=d["s"])
+    assert len(gen._programs) == n1 and n1 <= n0 + 1
+    assert (wavs[0].cpu() - d["wav"]).abs().max().item() < 1e-3
+    wavs, ss = gen.inference_batch([d["mel"]], phase_vec=d["phase_vec"], noise=d["noise"])
+    assert (ss[0].cpu() - d["s"]).abs().max().item() < 3e-4
+    assert (wavs[0].cpu() - d["wav"]).abs().max().item() < 2e-3

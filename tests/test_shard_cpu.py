@@ -52,3 +52,16 @@ def _worker(rank, world, port, n_total):
 
 def test_gather_over_gloo_world2():
     mp.spawn(_worker, args=(2, 29533, 23), nprocs=2, join=True)
+
+
+def test_batches_are_single_stride_bucket_and_patterns_repeat():
+    import random
+    rnd = random.Random(3)
+    lens = [281 + rnd.randint(188, 2812) for _ in range(512)]
+    batches = shard.make_batches(range(512), lens, row_budget=48 * 1024, align=256)
+    patterns = set()
+    for b in batches:
+        strides = {(lens[i] + 8 + 255) // 256 * 256 for i in b}
+        assert len(strides) == 1
+        patterns.add((strides.pop(), len(b)))
+    assert len(patterns) <= 2 * 12            # <= one full + one partial pattern per 256-row bucket
