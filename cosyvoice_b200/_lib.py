@@ -76,6 +76,7 @@ _SPECIAL = {
     "cvb200_last_error": ([], C.c_char_p),
     "cvb200_version": ([], C.c_int),
     "cvb200_launch_count": ([], C.c_int64),
+    "cvb200_set_pdl": ([C.c_int], C.c_int),
 }
 
 _lib = None

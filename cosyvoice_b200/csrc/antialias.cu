@@ -189,6 +189,7 @@ __global__ void __launch_bounds__(128) aa_rows_kernel(const void* __restrict__ x
                                                       const float* __restrict__ filt, const float* __restrict__ alpha,
                                                       const float* __restrict__ beta, int C, const Layout lay,
                                                       long long n_items) {
+  pdl_sync();
   constexpr bool FAST = ODT == CVB200_BF16;
   const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= n_items) return;
@@ -254,6 +255,7 @@ __global__ void __launch_bounds__(NC_THREADS) aa_nct_kernel(const void* __restri
                                                             long long n_rows, const float* __restrict__ fu,
                                                             const float* __restrict__ fd, const float* __restrict__ alpha,
                                                             const float* __restrict__ beta) {
+  pdl_sync();
   constexpr bool FAST = DT == CVB200_BF16;
   extern __shared__ float nc_smem[];
   float* sx0 = nc_smem;
@@ -334,7 +336,7 @@ int launch_anti_alias_rows(const void* x, int ldx, int x_dt, void* out, int ldo,
   const long long n_items = (long long)(lay.rows / AA_TS) * (C / 2);
   const unsigned grid = (unsigned)((n_items + 127) / 128);
 #define AA_ROWS(XD, OD)                                                                                        \
-  aa_rows_kernel<XD, OD><<<grid, 128, 0, st>>>(x, ldx, out, ldo, filt, alpha, beta, C, lay, n_items)
+  CVB_CUDA(launch_pdl(aa_rows_kernel<XD, OD>, dim3(grid), dim3(128), 0, st, x, ldx, out, ldo, filt, alpha, beta, C, lay, n_items))
   if (x_dt == CVB200_F32 && out_dt == CVB200_BF16) AA_ROWS(CVB200_F32, CVB200_BF16);
   else if (x_dt == CVB200_F32 && out_dt == CVB200_F32) AA_ROWS(CVB200_F32, CVB200_F32);
   else if (x_dt == CVB200_BF16 && out_dt == CVB200_BF16) AA_ROWS(CVB200_BF16, CVB200_BF16);
@@ -357,9 +359,9 @@ int launch_anti_alias_nct(const void* x, void* y, int dt, int B, int C, int T, c
   }
   dim3 grid((unsigned)ceil_div(T, NC_N), (unsigned)((n_rows + 1) / 2));
   if (dt == CVB200_BF16)
-    aa_nct_kernel<CVB200_BF16><<<grid, NC_THREADS, NC_SMEM, st>>>(x, y, C, T, n_rows, fu, fd, alpha, beta);
+    CVB_CUDA(launch_pdl(aa_nct_kernel<CVB200_BF16>, dim3(grid), dim3(NC_THREADS), NC_SMEM, st, x, y, C, T, n_rows, fu, fd, alpha, beta));
   else
-    aa_nct_kernel<CVB200_F32><<<grid, NC_THREADS, NC_SMEM, st>>>(x, y, C, T, n_rows, fu, fd, alpha, beta);
+    CVB_CUDA(launch_pdl(aa_nct_kernel<CVB200_F32>, dim3(grid), dim3(NC_THREADS), NC_SMEM, st, x, y, C, T, n_rows, fu, fd, alpha, beta));
   CVB_LAUNCH_CHECK();
   return CVB_OK;
 }

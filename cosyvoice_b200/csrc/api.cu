@@ -14,6 +14,18 @@ void set_last_error(const std::string& msg) { g_last_error = msg; }
 const char* get_last_error() { return g_last_error.c_str(); }
 void count_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
 
+static std::atomic<int> g_pdl{-1};
+bool pdl_enabled() {
+  int v = g_pdl.load(std::memory_order_relaxed);
+  if (v < 0) {
+    const char* e = getenv("CVB200_PDL");
+    v = (e && e[0] == '0') ? 0 : 1;
+    g_pdl.store(v, std::memory_order_relaxed);
+  }
+  return v != 0;
+}
+void set_pdl_enabled(bool on) { g_pdl.store(on ? 1 : 0, std::memory_order_relaxed); }
+
 using Layout = cvb200_layout;
 int launch_layernorm(const float*, int, void*, int, int, const float*, const float*, int, int, float, cudaStream_t);
 int launch_norm_mish(const void*, int, int, void*, int, int, const float*, const float*, const double*, const float*, int,
@@ -59,6 +71,11 @@ extern "C" {
 const char* cvb200_last_error(void) { return get_last_error(); }
 int cvb200_version(void) { return 100; }
 int64_t cvb200_launch_count(void) { return (int64_t)g_launches.load(); }
+int cvb200_set_pdl(int on) {
+  const int prev = pdl_enabled() ? 1 : 0;
+  set_pdl_enabled(on != 0);
+  return prev;
+}
 
 int cvb200_tapgemm(const cvb200_gemm* p, int engine, void* stream) {
   NEED(p, "gemm descriptor");

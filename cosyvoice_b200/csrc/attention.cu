@@ -66,6 +66,7 @@ __device__ __forceinline__ void load_tile(uint32_t tile_base, const __nv_bfloat1
 __global__ void __launch_bounds__(128) attention_bf16_kernel(const __nv_bfloat16* __restrict__ qkv, int ld,
                                                              __nv_bfloat16* __restrict__ out, int ldo, const Layout lay,
                                                              int heads, float scale_log2) {
+  pdl_sync();
   extern __shared__ __align__(128) uint8_t smem[];
   const int tile = blockIdx.x, head = blockIdx.y;
   const int b = __ldg(lay.tile_seq + tile);
@@ -238,6 +239,7 @@ __global__ void __launch_bounds__(128) attention_bf16_kernel(const __nv_bfloat16
 // 128 threads = 128 queries of one tile; K/V blocks of 32 keys staged in shared memory.
 __global__ void __launch_bounds__(128) attention_f32_kernel(const float* __restrict__ qkv, int ld, float* __restrict__ out,
                                                             int ldo, const Layout lay, int heads, float scale) {
+  pdl_sync();
   __shared__ float sK[32][HD];
   __shared__ float sV[32][HD];
   const int tile = blockIdx.x, head = blockIdx.y;
@@ -324,12 +326,12 @@ int launch_attention(const void* qkv, int ld, void* out, int ldo, int dt, const 
       CVB_CUDA(cudaFuncSetAttribute(attention_bf16_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM));
       attr_done = true;
     }
-    attention_bf16_kernel<<<grid, 128, SMEM, st>>>(reinterpret_cast<const __nv_bfloat16*>(qkv), ld,
+    CVB_CUDA(launch_pdl(attention_bf16_kernel, dim3(grid), dim3(128), SMEM, st, reinterpret_cast<const __nv_bfloat16*>(qkv), ld,
                                                    reinterpret_cast<__nv_bfloat16*>(out), ldo, lay, heads,
-                                                   scale * 1.4426950408889634f);
+                                                   scale * 1.4426950408889634f));
   } else {
-    attention_f32_kernel<<<grid, 128, 0, st>>>(reinterpret_cast<const float*>(qkv), ld, reinterpret_cast<float*>(out), ldo,
-                                               lay, heads, scale);
+    CVB_CUDA(launch_pdl(attention_f32_kernel, dim3(grid), dim3(128), 0, st, reinterpret_cast<const float*>(qkv), ld, reinterpret_cast<float*>(out), ldo,
+                                               lay, heads, scale));
   }
   CVB_LAUNCH_CHECK();
   return CVB_OK;

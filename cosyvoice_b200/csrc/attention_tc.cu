@@ -100,6 +100,8 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tm, __nv_bfloat16* __res
   __syncthreads();
   ptx::tc_fence_after();
   const uint32_t tmem = *tmem_slot;
+  pdl_trigger();      // programmatic dependent launch: the prologue above overlapped the previous kernel's tail
+  pdl_wait();
 
   if (warp == 0) {
     if (lane == 0) {
@@ -292,8 +294,8 @@ int launch_attention_tc(const void* qkv, int ld, void* out, int ldo, const Layou
   });
   CVB_CUDA(attr_err);
   const int grid = (lay.rows / 128) * heads;
-  attention_tc_kernel<<<grid, 320, SMEM_BYTES, st>>>(tm, reinterpret_cast<__nv_bfloat16*>(out), ldo, lay, heads,
-                                                     scale * 1.4426950408889634f);
+  CVB_CUDA(launch_pdl(attention_tc_kernel, dim3(grid), dim3(320), SMEM_BYTES, st, tm, reinterpret_cast<__nv_bfloat16*>(out), ldo, lay, heads,
+                                                     scale * 1.4426950408889634f));
   CVB_LAUNCH_CHECK();
   return CVB_OK;
 }

@@ -50,6 +50,39 @@ void count_launch();
     CVB_CUDA(cudaGetLastError()); \
   } while (0)
 
+// ---------------------------------------------------------------- programmatic dependent launch
+// Every kernel of the library is launched with the programmatic-stream-serialization attribute and begins with
+// pdl_sync(): the next kernel's CTAs may be scheduled (and run their prologue: barrier init, TMEM allocation,
+// tensor-map prefetch) while the previous grid drains, but touch global memory only after it has fully completed.
+// The estimator is ~540 dependent launches per call, so the launch gap matters for chunk latency.
+bool pdl_enabled();
+void set_pdl_enabled(bool on);
+
+#ifdef __CUDACC__
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_sync() {
+  pdl_trigger();
+  pdl_wait();
+}
+
+template <class... KArgs, class... Args>
+inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st,
+                              Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = pdl_enabled() ? 1 : 0;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  return cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
+}
+#endif
+
 // ---------------------------------------------------------------- dtypes
 // Activation/weight storage type of a run: fp32 (parity mode, CUDA cores) or bf16 (tensor cores).
 enum DType : int { DT_F32 = 0, DT_BF16 = 1 };

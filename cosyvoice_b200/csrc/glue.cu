@@ -47,6 +47,7 @@ __device__ __forceinline__ void load8_dt(const void* base, size_t idx, int dt, f
 __global__ void __launch_bounds__(256) layernorm256_kernel(const float* __restrict__ x, int ldx, void* __restrict__ out,
                                                            int ldo, int out_dt, const float* __restrict__ gamma,
                                                            const float* __restrict__ beta, int rows, float eps) {
+  pdl_sync();
   const int row = blockIdx.x * 8 + (threadIdx.x >> 5);
   const int lane = threadIdx.x & 31;
   if (row >= rows) return;
@@ -75,6 +76,7 @@ __global__ void __launch_bounds__(256) norm_mish256_kernel(const void* __restric
                                                            const double* __restrict__ gn_stats,
                                                            const float* __restrict__ seq_bias, int seq_bias_ld,
                                                            const Layout lay, float eps) {
+  pdl_sync();
   const int row = blockIdx.x * 8 + (threadIdx.x >> 5);
   const int lane = threadIdx.x & 31;
   if (row >= lay.rows) return;
@@ -129,6 +131,7 @@ __global__ void __launch_bounds__(256) norm_mish256_kernel(const void* __restric
 
 // ---------------------------------------------------------------------------- time embedding
 __global__ void time_sinusoid_kernel(const float* __restrict__ t, int S, int dim, float scale, float* __restrict__ out) {
+  pdl_sync();
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   const int half = dim / 2;
   if (i >= S * half) return;
@@ -153,6 +156,7 @@ __device__ __forceinline__ float small_act(int act, float v) {
 __global__ void __launch_bounds__(256) small_linear_kernel(const float* __restrict__ x, int S, int K,
                                                            const float* __restrict__ W, const float* __restrict__ b,
                                                            int N, int pre_act, int post_act, float* __restrict__ y) {
+  pdl_sync();
   const int n = blockIdx.x * 8 + (threadIdx.x >> 5);
   const int lane = threadIdx.x & 31;
   if (n >= N) return;
@@ -176,6 +180,7 @@ __global__ void __launch_bounds__(256) small_linear_kernel(const float* __restri
 __global__ void __launch_bounds__(256) pack_cfg_kernel(const float* __restrict__ x, const float* __restrict__ mu,
                                                        const float* __restrict__ cond, const float* __restrict__ spks,
                                                        void* __restrict__ out, int out_dt, const Layout lay) {
+  pdl_sync();
   // one thread per (row of the pair layout, 8-channel chunk): 320 / 8 = 40 chunks per row
   const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   const long long total = 2LL * lay.rows * 40;
@@ -205,6 +210,7 @@ __global__ void __launch_bounds__(256) pack_cfg_kernel(const float* __restrict__
 
 __global__ void __launch_bounds__(256) euler_cfg_kernel(float* __restrict__ x, const float* __restrict__ v, long long n4,
                                                         float dt, float cfg) {
+  pdl_sync();
   const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n4) return;
   float4 xv = reinterpret_cast<float4*>(x)[i];
@@ -223,6 +229,7 @@ __global__ void __launch_bounds__(256) euler_cfg_kernel(float* __restrict__ x, c
 __global__ void __launch_bounds__(256) nct_to_rows_kernel(const float* __restrict__ src, long long seq_stride,
                                                           long long c_stride, int C, void* __restrict__ out, int ldo,
                                                           int out_dt, const Layout lay) {
+  pdl_sync();
   __shared__ float tile[32][33];
   const int r0 = blockIdx.x * 32, c0 = blockIdx.y * 32;
   const int t128 = r0 >> 7;
@@ -244,6 +251,7 @@ __global__ void __launch_bounds__(256) nct_to_rows_kernel(const float* __restric
 __global__ void __launch_bounds__(256) rows_to_nct_kernel(const float* __restrict__ src, int lds, int C,
                                                           float* __restrict__ out, long long seq_stride,
                                                           long long c_stride, const Layout lay) {
+  pdl_sync();
   __shared__ float tile[32][33];
   const int r0 = blockIdx.x * 32, c0 = blockIdx.y * 32;
   const int t128 = r0 >> 7;
@@ -268,7 +276,7 @@ int launch_layernorm(const float* x, int ldx, void* out, int ldo, int out_dt, co
   CVB_REQUIRE(C == 256, "LayerNorm kernel is specialised for 256 channels");
   CVB_REQUIRE(ldx % 4 == 0 && ldo % 8 == 0, "leading dimensions must keep 16-byte alignment");
   if (rows <= 0) return CVB_OK;
-  layernorm256_kernel<<<ceil_div(rows, 8), 256, 0, st>>>(x, ldx, out, ldo, out_dt, gamma, beta, rows, eps);
+  CVB_CUDA(launch_pdl(layernorm256_kernel, dim3(ceil_div(rows, 8)), dim3(256), 0, st, x, ldx, out, ldo, out_dt, gamma, beta, rows, eps));
   CVB_LAUNCH_CHECK();
   return CVB_OK;
 }
@@ -279,8 +287,8 @@ int launch_norm_mish(const void* h, int ldh, int h_dt, void* out, int ldo, int o
   CVB_REQUIRE(C == 256, "Norm+Mish kernel is specialised for 256 channels");
   CVB_REQUIRE(ldh % 8 == 0 && ldo % 8 == 0, "leading dimensions must keep 16-byte alignment");
   if (lay.rows <= 0) return CVB_OK;
-  norm_mish256_kernel<<<ceil_div(lay.rows, 8), 256, 0, st>>>(h, ldh, h_dt, out, ldo, out_dt, gamma, beta, gn_stats,
-                                                             seq_bias, seq_bias_ld, lay, eps);
+  CVB_CUDA(launch_pdl(norm_mish256_kernel, dim3(ceil_div(lay.rows, 8)), dim3(256), 0, st, h, ldh, h_dt, out, ldo, out_dt, gamma, beta, gn_stats,
+                                                             seq_bias, seq_bias_ld, lay, eps));
   CVB_LAUNCH_CHECK();
   return CVB_OK;
 }
@@ -289,7 +297,7 @@ int launch_time_sinusoid(const float* t, int S, int dim, float scale, float* out
   CVB_REQUIRE(dim % 2 == 0 && dim >= 4, "dim must be even");
   if (S <= 0) return CVB_OK;
   const int n = S * dim / 2;
-  time_sinusoid_kernel<<<ceil_div(n, 128), 128, 0, st>>>(t, S, dim, scale, out);
+  CVB_CUDA(launch_pdl(time_sinusoid_kernel, dim3(ceil_div(n, 128)), dim3(128), 0, st, t, S, dim, scale, out));
   CVB_LAUNCH_CHECK();
   return CVB_OK;
 }
@@ -298,7 +306,7 @@ int launch_small_linear(const float* x, int S, int K, const float* W, const floa
                         float* y, cudaStream_t st) {
   CVB_REQUIRE(K % 32 == 0 && K <= 1024, "K must be a multiple of 32 and <= 1024");
   if (S <= 0 || N <= 0) return CVB_OK;
-  small_linear_kernel<<<ceil_div(N, 8), 256, 0, st>>>(x, S, K, W, b, N, pre_act, post_act, y);
+  CVB_CUDA(launch_pdl(small_linear_kernel, dim3(ceil_div(N, 8)), dim3(256), 0, st, x, S, K, W, b, N, pre_act, post_act, y));
   CVB_LAUNCH_CHECK();
   return CVB_OK;
 }
@@ -307,7 +315,7 @@ int launch_pack_cfg(const float* x, const float* mu, const float* cond, const fl
                     const Layout& lay, cudaStream_t st) {
   const long long total = 2LL * lay.rows * 40;
   if (total <= 0) return CVB_OK;
-  pack_cfg_kernel<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(x, mu, cond, spks, out, out_dt, lay);
+  CVB_CUDA(launch_pdl(pack_cfg_kernel, dim3((unsigned)((total + 255) / 256)), dim3(256), 0, st, x, mu, cond, spks, out, out_dt, lay));
   CVB_LAUNCH_CHECK();
   return CVB_OK;
 }
@@ -316,7 +324,7 @@ int launch_euler_cfg(float* x, const float* v, long long n_half, float dt, float
   CVB_REQUIRE(n_half % 4 == 0, "element count must be a multiple of 4");
   const long long n4 = n_half / 4;
   if (n4 <= 0) return CVB_OK;
-  euler_cfg_kernel<<<(unsigned)((n4 + 255) / 256), 256, 0, st>>>(x, v, n4, dt, cfg);
+  CVB_CUDA(launch_pdl(euler_cfg_kernel, dim3((unsigned)((n4 + 255) / 256)), dim3(256), 0, st, x, v, n4, dt, cfg));
   CVB_LAUNCH_CHECK();
   return CVB_OK;
 }
@@ -325,7 +333,7 @@ int launch_nct_to_rows(const float* src, long long seq_stride, long long c_strid
                        const Layout& lay, cudaStream_t st) {
   if (lay.rows <= 0) return CVB_OK;
   dim3 grid(lay.rows / 32, ceil_div(C, 32));
-  nct_to_rows_kernel<<<grid, 256, 0, st>>>(src, seq_stride, c_stride, C, out, ldo, out_dt, lay);
+  CVB_CUDA(launch_pdl(nct_to_rows_kernel, dim3(grid), dim3(256), 0, st, src, seq_stride, c_stride, C, out, ldo, out_dt, lay));
   CVB_LAUNCH_CHECK();
   return CVB_OK;
 }
@@ -334,7 +342,7 @@ int launch_rows_to_nct(const float* src, int lds, int C, float* out, long long s
                        const Layout& lay, cudaStream_t st) {
   if (lay.rows <= 0) return CVB_OK;
   dim3 grid(lay.rows / 32, ceil_div(C, 32));
-  rows_to_nct_kernel<<<grid, 256, 0, st>>>(src, lds, C, out, seq_stride, c_stride, lay);
+  CVB_CUDA(launch_pdl(rows_to_nct_kernel, dim3(grid), dim3(256), 0, st, src, lds, C, out, seq_stride, c_stride, lay));
   CVB_LAUNCH_CHECK();
   return CVB_OK;
 }

@@ -10,6 +10,7 @@ constexpr int BM = TILE_M, BN = 64, BK = 16, NT = 256;
 
 template <typename T>
 __global__ void __launch_bounds__(NT) tapgemm_simt_kernel(const GemmParams p) {
+  pdl_sync();
   __shared__ float As[BK][BM + 4];
   __shared__ float Ws[BK][BN + 4];
   const int tile = blockIdx.x, nt = blockIdx.y, phase = blockIdx.z;
@@ -107,8 +108,8 @@ int launch_tapgemm_simt(const GemmParams& p, cudaStream_t stream) {
   CVB_REQUIRE(p.m_tiles > 0, "empty problem");
   CVB_TRY(check_epilogue_layout(p));
   dim3 grid(p.m_tiles, ceil_div(p.n_pad, BN), p.n_phase);
-  if (p.dt == DT_BF16) tapgemm_simt_kernel<__nv_bfloat16><<<grid, NT, 0, stream>>>(p);
-  else tapgemm_simt_kernel<float><<<grid, NT, 0, stream>>>(p);
+  if (p.dt == DT_BF16) CVB_CUDA(launch_pdl(tapgemm_simt_kernel<__nv_bfloat16>, dim3(grid), dim3(NT), 0, stream, p));
+  else CVB_CUDA(launch_pdl(tapgemm_simt_kernel<float>, dim3(grid), dim3(NT), 0, stream, p));
   CVB_LAUNCH_CHECK();
   return CVB_OK;
 }

@@ -102,6 +102,10 @@ tapgemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
   __syncthreads();
   ptx::tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  // Programmatic dependent launch: everything above (and the weight preload below: W is a constant of the model,
+  // never written by a kernel) overlaps the tail of the previous kernel; activations are touched after pdl_wait().
+  pdl_trigger();
+  if (warp != 0) pdl_wait();
 
   if (warp == 0) {
     // ------------------------------------------------------------------ TMA producer
@@ -115,6 +119,7 @@ tapgemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
         for (int kb = 0; kb < kblocks; ++kb)
           ptx::tma_load_2d(sB + kb * w_box_bytes, &tmW, w_full, kb * GEMM_BK, key_phase * p.n_pad + key_nt * bn);
       }
+      pdl_wait();
       for (int it = it0; it < it_end; it += it_step) {
         int mt, phase, nt;
         decode(it, mt, phase, nt);
@@ -284,7 +289,7 @@ int launch_tapgemm_tc(const GemmParams& p, cudaStream_t stream) {
   } else {
     grid = total < sms ? total : sms;
   }
-  tapgemm_tc_kernel<<<grid, NUM_THREADS, SMEM_BYTES, stream>>>(tmA, tmW, p, resident ? 1 : 0);
+  CVB_CUDA(launch_pdl(tapgemm_tc_kernel, dim3(grid), dim3(NUM_THREADS), SMEM_BYTES, stream, tmA, tmW, p, resident ? 1 : 0));
   CVB_LAUNCH_CHECK();
   return CVB_OK;
 }

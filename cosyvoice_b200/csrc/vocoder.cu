@@ -26,6 +26,7 @@ __device__ __forceinline__ bool row_info(const Layout& lay, int row, int& b, int
 __global__ void __launch_bounds__(256) rowdot_abs_kernel(const void* __restrict__ x, int ldx, int x_dt,
                                                          const float* __restrict__ w, const float* __restrict__ bias, int K,
                                                          float* __restrict__ out, int rows) {
+  pdl_sync();
   const int row = blockIdx.x * 8 + (threadIdx.x >> 5);
   const int lane = threadIdx.x & 31;
   if (row >= rows) return;
@@ -39,6 +40,7 @@ __global__ void __launch_bounds__(256) rowdot_abs_kernel(const void* __restrict_
 // exclusive prefix (in cycles, fp64) of hop * f0 / sr over the frames of each sequence; one warp per sequence.
 __global__ void __launch_bounds__(32) f0_prefix_kernel(const float* __restrict__ f0, const Layout lay, double cycles_per_hz,
                                                        double* __restrict__ prefix) {
+  pdl_sync();
   const int b = blockIdx.x, lane = threadIdx.x;
   const int len = lay.seq_len[b];
   const long long r0 = lay.seq_row0[b];
@@ -65,6 +67,7 @@ __global__ void __launch_bounds__(256) sine_source_kernel(const float* __restric
                                                           const float* __restrict__ noise, const float* __restrict__ phase,
                                                           const float* __restrict__ lin_w, const float* __restrict__ lin_b,
                                                           float* __restrict__ s, long long l_max) {
+  pdl_sync();
   const int b = blockIdx.y;
   const long long n = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   const int len = __ldg(lay.seq_len + b);
@@ -90,6 +93,7 @@ __global__ void __launch_bounds__(256) sine_source_kernel(const float* __restric
 // ------------------------------------------------------------------ STFT (n_fft 16, hop 4)
 __global__ void __launch_bounds__(256) stft16_kernel(const float* __restrict__ s, long long l_max, void* __restrict__ out,
                                                      int ldo, int out_dt, const Layout lay) {
+  pdl_sync();
   __shared__ float cs[16], sn[16], win[16];
   if (threadIdx.x < 16) {
     float sv, cv;
@@ -139,6 +143,7 @@ __global__ void __launch_bounds__(256) stft16_kernel(const float* __restrict__ s
 // one thread per hop (4 output samples); frames q-1 .. q+2 overlap it.
 __global__ void __launch_bounds__(128) istft16_kernel(const float* __restrict__ x, int ldx, const Layout lay,
                                                       float* __restrict__ wav, long long l_max, float limit) {
+  pdl_sync();
   __shared__ float cs[16], sn[16], win[16];
   if (threadIdx.x < 16) {
     float sv, cv;
@@ -193,6 +198,7 @@ __global__ void __launch_bounds__(128) istft16_kernel(const float* __restrict__ 
 __global__ void __launch_bounds__(256) snake_kernel(const void* __restrict__ x, int ldx, int x_dt, void* __restrict__ out,
                                                     int ldo, int out_dt, const float* __restrict__ alpha, int C,
                                                     const Layout lay) {
+  pdl_sync();
   const int cpr = C / 4;                           // 4-channel chunks per row
   const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= (long long)lay.rows * cpr) return;
@@ -221,6 +227,7 @@ __global__ void __launch_bounds__(256) snake_kernel(const void* __restrict__ x, 
 }
 
 __global__ void reflect_row0_kernel(void* __restrict__ x, int ldx, int dt, int C, const Layout lay) {
+  pdl_sync();
   const int b = blockIdx.x;
   if (__ldg(lay.seq_len + b) < 3) return;
   const size_t r0 = (size_t)__ldg(lay.seq_row0 + b);
@@ -234,7 +241,7 @@ __global__ void reflect_row0_kernel(void* __restrict__ x, int ldx, int dt, int C
 int launch_rowdot_abs(const void* x, int ldx, int x_dt, const float* w, const float* b, int K, float* out, int rows,
                       cudaStream_t st) {
   if (rows <= 0) return CVB_OK;
-  rowdot_abs_kernel<<<ceil_div(rows, 8), 256, 0, st>>>(x, ldx, x_dt, w, b, K, out, rows);
+  CVB_CUDA(launch_pdl(rowdot_abs_kernel, dim3(ceil_div(rows, 8)), dim3(256), 0, st, x, ldx, x_dt, w, b, K, out, rows));
   CVB_LAUNCH_CHECK();
   return CVB_OK;
 }
@@ -245,11 +252,11 @@ int launch_sine_source(const float* f0, const Layout& lay0, int hop, float sr, c
   CVB_REQUIRE(hop > 0 && sr > 0.f, "bad hop / sample rate");
   CVB_REQUIRE((long long)lay0.max_len * hop <= l_max, "l_max smaller than the longest utterance");
   if (lay0.n_seq <= 0) return CVB_OK;
-  f0_prefix_kernel<<<lay0.n_seq, 32, 0, st>>>(f0, lay0, (double)hop / (double)sr, prefix_ws);
+  CVB_CUDA(launch_pdl(f0_prefix_kernel, dim3(lay0.n_seq), dim3(32), 0, st, f0, lay0, (double)hop / (double)sr, prefix_ws));
   CVB_LAUNCH_CHECK();
   const long long nmax = (long long)lay0.max_len * hop;
   dim3 grid((unsigned)((nmax + 255) / 256), lay0.n_seq);
-  sine_source_kernel<<<grid, 256, 0, st>>>(f0, prefix_ws, lay0, hop, 1.0 / (double)sr, noise, phase, lin_w, lin_b, s, l_max);
+  CVB_CUDA(launch_pdl(sine_source_kernel, dim3(grid), dim3(256), 0, st, f0, prefix_ws, lay0, hop, 1.0 / (double)sr, noise, phase, lin_w, lin_b, s, l_max));
   CVB_LAUNCH_CHECK();
   return CVB_OK;
 }
@@ -257,7 +264,7 @@ int launch_sine_source(const float* f0, const Layout& lay0, int hop, float sr, c
 int launch_stft16(const float* s, long long l_max, void* out, int ldo, int out_dt, const Layout& lay, cudaStream_t st) {
   CVB_REQUIRE(ldo >= 18, "stft output needs 18 columns");
   if (lay.rows <= 0) return CVB_OK;
-  stft16_kernel<<<ceil_div(lay.rows, 256), 256, 0, st>>>(s, l_max, out, ldo, out_dt, lay);
+  CVB_CUDA(launch_pdl(stft16_kernel, dim3(ceil_div(lay.rows, 256)), dim3(256), 0, st, s, l_max, out, ldo, out_dt, lay));
   CVB_LAUNCH_CHECK();
   return CVB_OK;
 }
@@ -265,7 +272,7 @@ int launch_stft16(const float* s, long long l_max, void* out, int ldo, int out_d
 int launch_istft16(const float* x, int ldx, const Layout& lay, float* wav, long long l_max, float limit, cudaStream_t st) {
   CVB_REQUIRE(ldx >= 18 && l_max % 4 == 0, "istft needs 18 columns and l_max % 4 == 0");
   if (lay.rows <= 0) return CVB_OK;
-  istft16_kernel<<<ceil_div(lay.rows, 128), 128, 0, st>>>(x, ldx, lay, wav, l_max, limit);
+  CVB_CUDA(launch_pdl(istft16_kernel, dim3(ceil_div(lay.rows, 128)), dim3(128), 0, st, x, ldx, lay, wav, l_max, limit));
   CVB_LAUNCH_CHECK();
   return CVB_OK;
 }
@@ -275,14 +282,14 @@ int launch_snake(const void* x, int ldx, int x_dt, void* out, int ldo, int out_d
   CVB_REQUIRE(C % 4 == 0 && ldo % 4 == 0, "C and ldo must be multiples of 4");
   const long long total = (long long)lay.rows * (C / 4);
   if (total <= 0) return CVB_OK;
-  snake_kernel<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(x, ldx, x_dt, out, ldo, out_dt, alpha, C, lay);
+  CVB_CUDA(launch_pdl(snake_kernel, dim3((unsigned)((total + 255) / 256)), dim3(256), 0, st, x, ldx, x_dt, out, ldo, out_dt, alpha, C, lay));
   CVB_LAUNCH_CHECK();
   return CVB_OK;
 }
 
 int launch_reflect_row0(void* x, int ldx, int dt, int C, const Layout& lay, cudaStream_t st) {
   if (lay.n_seq <= 0) return CVB_OK;
-  reflect_row0_kernel<<<lay.n_seq, 128, 0, st>>>(x, ldx, dt, C, lay);
+  CVB_CUDA(launch_pdl(reflect_row0_kernel, dim3(lay.n_seq), dim3(128), 0, st, x, ldx, dt, C, lay));
   CVB_LAUNCH_CHECK();
   return CVB_OK;
 }

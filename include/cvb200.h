@@ -129,6 +129,9 @@ const char* cvb200_last_error(void);
 int cvb200_version(void);
 /* number of kernels this library has launched in this process (bench.py's gpu_launches) */
 int64_t cvb200_launch_count(void);
+/* programmatic dependent launch of the library's kernels (default on; env CVB200_PDL=0 turns it off).  Returns the
+ * previous setting.  Kernels launched while a CUDA graph is being captured keep the setting of capture time. */
+int cvb200_set_pdl(int on);
 
 int cvb200_tapgemm(const cvb200_gemm* p, int engine, void* stream);
 
