@@ -258,7 +258,8 @@ int num_sms() {
 
 }  // namespace
 
-int launch_tapgemm_tc(const GemmParams& p, cudaStream_t stream) {
+int launch_tapgemm_tc(const GemmParams& p_in, cudaStream_t stream) {
+  GemmParams p = p_in;
   CVB_REQUIRE(p.dt == DT_BF16, "tcgen05 engine needs bf16 operands");
   CVB_REQUIRE(p.seg_len % GEMM_BK == 0, "seg_len must be a multiple of 64");
   CVB_REQUIRE(p.n_phase * p.n_seg <= MAX_SEGS, "too many segments");
@@ -266,6 +267,10 @@ int launch_tapgemm_tc(const GemmParams& p, cudaStream_t stream) {
   CVB_REQUIRE(p.bn >= 16 && p.bn <= 256 && p.bn % 16 == 0 && p.n_pad % p.bn == 0, "bad N tile");
   CVB_REQUIRE(!p.epi.gn_stats || p.bn % 32 == 0, "GroupNorm statistics need bn % 32 == 0");
   CVB_TRY(check_epilogue_layout(p));
+  const int sms = num_sms();
+  // Latency mode (streaming chunks: a handful of 128-row tiles): narrower N tiles put the problem on more SMs.
+  // Each CTA then streams a quarter of the weights; the A tile is re-read from L2 by its N-tile siblings.
+  while (p.bn % 128 == 0 && 2LL * p.m_tiles * p.n_phase * (p.n_pad / p.bn) <= sms) p.bn /= 2;
   static std::once_flag attr_once;
   static cudaError_t attr_err = cudaSuccess;
   std::call_once(attr_once, [] {
@@ -278,7 +283,6 @@ int launch_tapgemm_tc(const GemmParams& p, cudaStream_t stream) {
   CVB_TRY(make_map_2d(&tmW, p.W, K, (uint64_t)p.n_phase * p.n_pad, K, GEMM_BK, (uint32_t)p.bn));
   const int keys = p.n_phase * (p.n_pad / p.bn);
   const int total = p.m_tiles * keys;
-  const int sms = num_sms();
   const bool resident = (uint64_t)p.bn * K * 2 <= (uint64_t)STAGES * B_STAGE_BYTES && keys <= sms &&
                         (p.bn * GEMM_BK * 2) % 1024 == 0;
   int grid;

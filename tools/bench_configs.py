@@ -68,6 +68,7 @@ def run_stream(args):
     dt = torch.bfloat16 if args.dtype == "bf16" else torch.float32
     est = B200Estimator(synthetic.flow_estimator_sd(True, seed=0), causal=True, dtype=dt, device=dev)
     cfm = B200CausalConditionalCFM(est)
+    cfm.use_cuda_graph = not args.eager
     hift = B200HiFTGenerator(synthetic.hift_sd(True, seed=1), v2=True, dtype=dt, device=dev)
     hop, prompt_tok, look = args.hop, 75, 3
     mel_cache, hop_samples = 8, hift.hop
@@ -273,6 +274,7 @@ def main():
     s.add_argument("--chunks", type=int, default=10)
     s.add_argument("--reps", type=int, default=5)
     s.add_argument("--dtype", default="bf16")
+    s.add_argument("--eager", action="store_true")
     b = sub.add_parser("bigvgan")
     b.add_argument("--batch", type=int, default=64)
     b.add_argument("--frames", default="94,938")
