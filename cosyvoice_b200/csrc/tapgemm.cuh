@@ -151,20 +151,19 @@ template <int NV> __device__ __forceinline__ void vec_store_dt(void* base, size_
   }
 }
 
-// exact-erf GELU with the Abramowitz-Stegun 7.1.26 rational approximation of erf (|error| <= 1.5e-7):
-// 2 MUFU + ~12 FMA-pipe instructions instead of erff's ~40 (the FFN-in epilogue is instruction-bound).
+// erf-GELU for the bf16 engine: x Phi(x) with Phi(x) = (1 + tanh(x (a + b x^2 + c x^4))) / 2, coefficients fitted to
+// the exact erf form on [-8, 8] (max abs error 2.5e-5, below the 4.9e-4 relative error of MUFU.TANH and far below
+// the bf16 rounding of the FFN hidden activations it feeds).  1 MUFU + 6 FMA-pipe instructions; the FFN-in
+// epilogue is instruction-bound (ncu: 27 -> 15 instructions per output).  The fp32 parity engine uses erff.
 __device__ __forceinline__ float gelu_erf_fast(float v) {
-  const float z = fabsf(v) * 0.70710678118654752f;
-  const float t = __fdividef(1.f, fmaf(0.3275911f, z, 1.f));
-  float poly = fmaf(1.061405429f, t, -1.453152027f);
-  poly = fmaf(poly, t, 1.421413741f);
-  poly = fmaf(poly, t, -0.284496736f);
-  poly = fmaf(poly, t, 0.254829592f);
-  poly *= t;
-  float e;
-  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(-1.4426950408889634f * z * z));
-  const float erf_abs = fmaf(-poly, e, 1.f);
-  return 0.5f * v * (1.f + copysignf(erf_abs, v));
+  const float xc = fminf(fmaxf(v, -6.f), 6.f);        // the fitted odd polynomial turns over beyond |x| ~ 10
+  const float x2 = xc * xc;
+  float p = fmaf(-3.51516916e-4f, x2, 3.70056467e-2f);
+  p = fmaf(p, x2, 7.97507884e-1f);
+  float t;
+  asm("tanh.approx.f32 %0, %1;" : "=f"(t) : "f"(xc * p));
+  const float h = 0.5f * v;
+  return fmaf(h, t, h);
 }
 
 template <int NV, bool PRECISE>
