@@ -7,7 +7,8 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "lib", "libcvb200.so")
+# CVB200_LIB: another build of the same library (A/B measurements of kernel changes on one GPU box)
+LIB_PATH = os.environ.get("CVB200_LIB") or os.path.join(_HERE, "lib", "libcvb200.so")
 
 F32, BF16 = 0, 1
 ENGINE_SIMT, ENGINE_TCGEN05 = 0, 1

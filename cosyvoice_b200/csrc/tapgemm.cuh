@@ -63,6 +63,21 @@ template <int NV> __device__ __forceinline__ void vec_add_f32(const float* p, fl
     v[j] += t.x; v[j + 1] += t.y; v[j + 2] += t.z; v[j + 3] += t.w;
   }
 }
+// 256-bit global load (sm_100+): a whole 32-byte sector per thread per instruction, so that the residual read of the
+// epilogue (each thread owns 64-128 contiguous bytes of a row) does not depend on L1 to merge half-sector accesses
+// (the GEMM CTA leaves ~25 KB of L1).  p must be 32-byte aligned.
+template <int NV> __device__ __forceinline__ void vec_add_f32_wide(const float* p, float (&v)[NV]) {
+  static_assert(NV % 8 == 0, "wide loads take 8 floats at a time");
+#pragma unroll
+  for (int j = 0; j < NV; j += 8) {
+    float t[8];
+    asm volatile("ld.global.v8.f32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+                 : "=f"(t[0]), "=f"(t[1]), "=f"(t[2]), "=f"(t[3]), "=f"(t[4]), "=f"(t[5]), "=f"(t[6]), "=f"(t[7])
+                 : "l"(p + j));
+#pragma unroll
+    for (int i = 0; i < 8; ++i) v[j + i] += t[i];
+  }
+}
 template <int NV> __device__ __forceinline__ void vec_add_bf16(const __nv_bfloat16* p, float (&v)[NV]) {
   if constexpr (NV % 8 == 0) {
 #pragma unroll
@@ -198,7 +213,10 @@ __device__ __forceinline__ void epi_apply(const Epi& e, size_t m, int b, bool va
     }
   }
   const size_t col = (size_t)phase * e.phase_col + n0;
-  if (e.res_kind == RES_F32) vec_add_f32<NV>(reinterpret_cast<const float*>(e.res) + m * e.ldr + col, v);
+  if (e.res_kind == RES_F32) {
+    if constexpr (NV % 16 == 0) vec_add_f32_wide<NV>(reinterpret_cast<const float*>(e.res) + m * e.ldr + col, v);
+    else vec_add_f32<NV>(reinterpret_cast<const float*>(e.res) + m * e.ldr + col, v);
+  }
   else if (e.res_kind == RES_ACT) vec_add_dt<NV>(e.res, m * e.ldr + col, e.res_dt, v);
   if (e.out_scale != 1.f) {
 #pragma unroll
@@ -246,6 +264,8 @@ inline int check_epilogue_layout(const GemmParams& p) {
   if (e.res_kind != RES_NONE) {
     const int sr = e.res_kind == RES_F32 ? 4 : dtype_size(e.res_dt);
     CVB_REQUIRE(e.res && al16(e.res) && (e.ldr * sr) % 16 == 0 && (e.phase_col * sr) % 16 == 0, "res alignment");
+    CVB_REQUIRE(e.res_kind != RES_F32 || (al32(e.res) && (e.ldr * 4) % 32 == 0 && (e.phase_col * 4) % 32 == 0),
+                "fp32 residual must keep 32-byte alignment");
   }
   CVB_REQUIRE(!e.bias || al16(e.bias), "bias must be 16-byte aligned (and padded to n_pad)");
   CVB_REQUIRE(!e.seq_bias || (al16(e.seq_bias) && e.seq_bias_ld % 4 == 0), "seq_bias alignment");

@@ -18,7 +18,10 @@ namespace cvb {
 
 namespace {
 
-constexpr int STAGES = 4;
+#ifndef CVB_GEMM_STAGES
+#define CVB_GEMM_STAGES 4
+#endif
+constexpr int STAGES = CVB_GEMM_STAGES;
 constexpr int A_STAGE_BYTES = TILE_M * GEMM_BK * 2;        // 16 KiB
 constexpr int B_STAGE_BYTES = 256 * GEMM_BK * 2;           // 32 KiB (bn <= 256)
 constexpr int BAR_BYTES = 256;
