@@ -45,6 +45,8 @@ int launch_stft16(const float*, long long, void*, int, int, const Layout&, cudaS
 int launch_istft16(const float*, int, const Layout&, float*, long long, float, cudaStream_t);
 int launch_snake(const void*, int, int, void*, int, int, const float*, int, const Layout&, cudaStream_t);
 int launch_reflect_row0(void*, int, int, int, const Layout&, cudaStream_t);
+int launch_ffn_fused(const void*, int, const void*, const float*, const void*, const float*, float*, int, void*, int,
+                     const cvb200_layout&, cudaStream_t);
 int launch_anti_alias_rows(const void*, int, int, void*, int, int, const float*, const float*, const float*, int,
                            const Layout&, cudaStream_t);
 int launch_anti_alias_nct(const void*, void*, int, int, int, int, const float*, const float*, const float*, const float*,
@@ -85,6 +87,12 @@ int cvb200_tapgemm(const cvb200_gemm* p, int engine, void* stream) {
   if (engine == CVB200_ENGINE_SIMT) return launch_tapgemm_simt(*p, ST(stream));
   set_last_error("invalid argument: unknown engine");
   return CVB_ERR_INVALID;
+}
+
+int cvb200_ffn_fused(const void* a, int lda, const void* w1, const float* b1, const void* w2, const float* b2, float* x,
+                     int ldx, void* out1, int ldo1, const cvb200_layout* lay, void* stream) {
+  CVB_REQUIRE(lay != nullptr, "null layout");
+  return launch_ffn_fused(a, lda, w1, b1, w2, b2, x, ldx, out1, ldo1, *lay, ST(stream));
 }
 
 int cvb200_layernorm(const float* x, int ldx, void* out, int ldo, int out_dt, const float* gamma, const float* beta,

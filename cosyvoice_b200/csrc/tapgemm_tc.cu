@@ -261,6 +261,13 @@ int num_sms() {
 
 }  // namespace
 
+// shared with the other tcgen05 kernels of the library (ffn_tc.cu)
+int make_map_2d_bf16(CUtensorMap* map, const void* base, uint64_t cols, uint64_t rows, uint64_t row_stride_elems,
+                     uint32_t box_cols, uint32_t box_rows) {
+  return make_map_2d(map, base, cols, rows, row_stride_elems, box_cols, box_rows);
+}
+int device_sm_count() { return num_sms(); }
+
 int launch_tapgemm_tc(const GemmParams& p_in, cudaStream_t stream) {
   GemmParams p = p_in;
   CVB_REQUIRE(p.dt == DT_BF16, "tcgen05 engine needs bf16 operands");

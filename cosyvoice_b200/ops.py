@@ -123,6 +123,25 @@ def gemm_op(plan: TapPlan, A: torch.Tensor, lay: SeqLayout, out0: torch.Tensor, 
     return _profiled("tapgemm_tc" if engine == _lib.ENGINE_TCGEN05 else "tapgemm_simt", flops, run)
 
 
+def ffn_fused_op(a: torch.Tensor, w1: torch.Tensor, b1: torch.Tensor, w2: torch.Tensor, b2: torch.Tensor,
+                 x: torch.Tensor, lay: SeqLayout, out1: Optional[torch.Tensor] = None, flops: int = 0) -> Op:
+    """x += W2 . gelu(W1 . a + b1) + b2 in one tcgen05 kernel (include/cvb200.h cvb200_ffn_fused)."""
+    _require_cuda(a, w1, b1, w2, b2, x, out1)
+    assert a.dtype == torch.bfloat16 and w1.dtype == torch.bfloat16 and w2.dtype == torch.bfloat16
+    assert x.dtype == torch.float32 and b1.dtype == torch.float32 and b2.dtype == torch.float32
+    assert tuple(w1.shape) == (1024, 256) and tuple(w2.shape) == (256, 1024) and w1.is_contiguous() and w2.is_contiguous()
+    assert out1 is None or out1.dtype == torch.bfloat16
+    lib = _lib.load()
+    layc = lay.c
+    args = (a.data_ptr(), a.stride(0), w1.data_ptr(), b1.data_ptr(), w2.data_ptr(), b2.data_ptr(), x.data_ptr(),
+            x.stride(0), _ptr(out1), out1.stride(0) if out1 is not None else 0, C.byref(layc))
+    keep = (a, w1, b1, w2, b2, x, out1, lay, layc)
+
+    def launch(_keep=keep):
+        _lib.check(lib.cvb200_ffn_fused(*args, _stream()), "ffn_fused")
+    return _profiled("gemm", flops, launch)
+
+
 def layernorm_op(x, out, gamma, beta, rows: int, eps: float = 1e-5) -> Op:
     _require_cuda(x, out)
     lib = _lib.load()

@@ -135,6 +135,15 @@ int cvb200_set_pdl(int on);
 
 int cvb200_tapgemm(const cvb200_gemm* p, int engine, void* stream);
 
+/* Fused FeedForward + residual of the estimator's BasicTransformerBlock (bf16 operands, tcgen05):
+ *   x[m, 0:256] += W2 . gelu(W1 . a[m, 0:256] + b1) + b2        cosyvoice/flow/components/transformer.py:83-136
+ *   (FeedForward: GELU(Linear 256->1024), Linear 1024->256), :309-314 (ff_output + hidden_states).
+ * a: bf16 [rows, lda] (the LayerNorm output), w1: bf16 [1024, 256], w2: bf16 [256, 1024] (nn.Linear layouts),
+ * b1 [1024], b2 [256] fp32, x: fp32 [rows, ldx] read and written in place, out1: optional bf16 [rows, ldo1] copy of
+ * the new x.  Rows past a sequence's valid length are written as zeros.  The hidden activations stay in TMEM. */
+int cvb200_ffn_fused(const void* a, int lda, const void* w1, const float* b1, const void* w2, const float* b2, float* x,
+                     int ldx, void* out1, int ldo1, const cvb200_layout* lay, void* stream);
+
 /* LayerNorm(256) over channels of each row: flow/components/transformer.py:195,231,262,300 */
 int cvb200_layernorm(const float* x, int ldx, void* out, int ldo, int out_dt, const float* gamma,
                      const float* beta, int rows, int C, float eps, void* stream);

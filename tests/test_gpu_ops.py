@@ -337,3 +337,37 @@ def test_snake_and_reflect():
     _sync()
     for b in range(2):
         assert torch.equal(x[lay.row0[b]], x[lay.row0[b] + 2])
+
+
+@pytest.mark.parametrize("lens", [[200, 77], [128], [1000, 3, 640, 129]])
+def test_ffn_fused_matches_torch(lens):
+    """cvb200_ffn_fused (hidden activations kept in TMEM) against torch on the same bf16-rounded operands:
+    x += W2 . bf16(gelu(W1 . a + b1)) + b2.  Tolerance = bf16 operand rounding of a K=1024 reduction."""
+    torch.manual_seed(31)
+    lay = SeqLayout.build(lens, DEV)
+    R = lay.rows
+    a = (torch.randn(R, 256, device=DEV)).to(torch.bfloat16)
+    w1 = (torch.randn(1024, 256, device=DEV) * (2.0 / 256) ** 0.5).to(torch.bfloat16)
+    w2 = (torch.randn(256, 1024, device=DEV) * (2.0 / 1024) ** 0.5).to(torch.bfloat16)
+    b1 = torch.randn(1024, device=DEV) * 0.1
+    b2 = torch.randn(256, device=DEV) * 0.1
+    x0 = torch.randn(R, 256, device=DEV)
+    x = x0.clone()
+    out1 = torch.full((R, 256), 7.0, device=DEV, dtype=torch.bfloat16)
+    ops.ffn_fused_op(a, w1, b1, w2, b2, x, lay, out1=out1)()
+    _sync()
+    h = torch.nn.functional.gelu(a.float() @ w1.float().t() + b1).to(torch.bfloat16).float()
+    want = x0 + h @ w2.float().t() + b2
+    for b, l in enumerate(lens):
+        r0 = lay.row0[b]
+        got = x[r0:r0 + l]
+        err = (got - want[r0:r0 + l]).abs().max().item()
+        assert err < 3e-2, (b, l, err)
+        assert (out1[r0:r0 + l].float() - got).abs().max().item() <= 2e-2 * max(1.0, got.abs().max().item())
+        assert x[r0 + l:r0 + lay.strides[b]].abs().max().item() == 0
+        assert out1[r0 + l:r0 + lay.strides[b]].float().abs().max().item() == 0
+    # second launch on the same buffers (barrier phases / TMEM reuse across launches)
+    x2 = x0.clone()
+    ops.ffn_fused_op(a, w1, b1, w2, b2, x2, lay)()
+    _sync()
+    assert torch.equal(x2, x)

@@ -74,6 +74,28 @@ def main():
         x1 = torch.randn(lay1.rows, 256, device=DEV).to(bf)
         plan = conv_transpose1d_plan(torch.randn(256, 128, 16) * .03, torch.randn(128), bf, DEV, stride=8, padding=4)
         bench("hift convT k16 s8 256->128 f32", plan, x1, lay1, xr)
+    def ffn_fused_case():
+        w1 = (torch.randn(1024, 256, device=DEV) * .06).to(bf)
+        w2 = (torch.randn(256, 1024, device=DEV) * .03).to(bf)
+        b1, b2 = torch.randn(1024, device=DEV), torch.randn(256, device=DEV)
+        op = ops.ffn_fused_op(z(256), w1, b1, w2, b2, X, lay)
+        flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=DEV)
+        for _ in range(3):
+            op()
+        torch.cuda.synchronize()
+        ms = 0.0
+        for _ in range(10):
+            flush.zero_()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            op()
+            e1.record()
+            torch.cuda.synchronize()
+            ms += e0.elapsed_time(e1)
+        ms /= 10
+        fl = 2 * 2 * 256 * 1024 * sum(lay.lens)
+        print(f"{'ffn fused 256->1024->256 +res':38s} M={lay.rows:8d} N=  256 K= 1024 phases=1  {ms * 1e3:9.1f} us  {fl / ms / 1e9:8.1f} TFLOP/s")
+    cases["ffn fused"] = ffn_fused_case
     for name, fn in cases.items():
         if a.only in name:
             fn()
