@@ -48,6 +48,17 @@ constexpr int FF_VEC_BYTES = (FF_H + FF_C) * 4;
 constexpr int FF_BAR_BYTES = 256;
 constexpr int FF_SMEM = 1024 + FF_A_BYTES + FF_STAGES * FF_STAGE_BYTES + FF_BAR_BYTES + FF_VEC_BYTES;
 
+#ifdef FFN_PROFILE
+#define FF_WAIT(acc, bar, par)             \
+  do {                                     \
+    const long long _t0 = clock64();       \
+    ptx::mbar_wait(bar, par);              \
+    acc += clock64() - _t0;                \
+  } while (0)
+#else
+#define FF_WAIT(acc, bar, par) ptx::mbar_wait(bar, par)
+#endif
+
 __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
   __nv_bfloat162 t = __floats2bfloat162_rn(lo, hi);
   return *reinterpret_cast<uint32_t*>(&t);
@@ -117,6 +128,17 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   pdl_wait();
 
   const int t_first = blockIdx.x, t_step = gridDim.x;
+#ifdef FFN_STAGGER
+  {   // experiment: spread the CTAs' phases so that their HBM-heavy drains do not coincide
+    const long long t0 = clock64();
+    const long long d = (long long)(blockIdx.x & 3) * FFN_STAGGER;
+    while (clock64() - t0 < d) {}
+  }
+#endif
+#ifdef FFN_PROFILE
+  long long prof[10] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
+  const long long t_start = clock64();
+#endif
 
   if (warp == 0) {
     // ------------------------------------------------------------------ TMA producer
@@ -126,7 +148,7 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       auto next_stage = [&]() { if (++stage == FF_STAGES) { stage = 0; ph ^= 1; } };
       auto load_g1 = [&](int c) {            // W1 rows [128c, +128): two stages of two [128 x 64] boxes
         for (int h = 0; h < 2; ++h) {
-          ptx::mbar_wait(&w_empty[stage], ph ^ 1);
+          FF_WAIT(prof[0], &w_empty[stage], ph ^ 1);
           ptx::mbar_arrive_expect_tx(&w_full[stage], FF_STAGE_BYTES);
           uint8_t* dst = sW + stage * FF_STAGE_BYTES;
           ptx::tma_load_2d(dst, &tmW1, &w_full[stage], (2 * h) * FF_BK, c * FF_CH);
@@ -136,7 +158,7 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       };
       auto load_g2 = [&](int c) {            // W2[:, 128c + 64j, +64): two stages of one [256 x 64] box
         for (int j = 0; j < 2; ++j) {
-          ptx::mbar_wait(&w_empty[stage], ph ^ 1);
+          FF_WAIT(prof[0], &w_empty[stage], ph ^ 1);
           ptx::mbar_arrive_expect_tx(&w_full[stage], FF_STAGE_BYTES);
           ptx::tma_load_2d(sW + stage * FF_STAGE_BYTES, &tmW2, &w_full[stage], c * FF_CH + j * FF_BK, 0);
           next_stage();
@@ -144,7 +166,7 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       };
       int n = 0;
       for (int t = t_first; t < m_tiles; t += t_step, ++n) {
-        if (n > 0) ptx::mbar_wait(a_free, (n - 1) & 1);
+        if (n > 0) FF_WAIT(prof[1], a_free, (n - 1) & 1);
         ptx::mbar_arrive_expect_tx(a_full, FF_A_BYTES);
         for (int kb = 0; kb < FF_C / FF_BK; ++kb)
           ptx::tma_load_2d(sA + kb * 16384, &tmA, a_full, kb * FF_BK, t * FF_M);
@@ -169,7 +191,7 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       auto issue_g1 = [&](int c) {
         const uint32_t d = tmem + FF_TM_H + (c & 1) * FF_CH;
         for (int h = 0; h < 2; ++h) {
-          ptx::mbar_wait(&w_full[stage], ph);
+          FF_WAIT(prof[2], &w_full[stage], ph);
           ptx::tc_fence_after();
           const uint32_t w_base = ptx::smem_u32(sW + stage * FF_STAGE_BYTES);
 #pragma unroll
@@ -185,20 +207,20 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       };
       int n = 0;
       for (int t = t_first; t < m_tiles; t += t_step, ++n) {
-        ptx::mbar_wait(a_full, n & 1);
+        FF_WAIT(prof[3], a_full, n & 1);
         ptx::tc_fence_after();
         issue_g1(0);
         for (int c = 0; c < FF_NCH; ++c) {
           if (c + 1 < FF_NCH) issue_g1(c + 1);
           else ptx::umma_commit(a_free);                         // all G1 of this tile are issued: A is free when they retire
           const int hb = c & 1;
-          ptx::mbar_wait(&p_full[hb], hcount[hb] & 1);
+          FF_WAIT(prof[4], &p_full[hb], hcount[hb] & 1);
           ++hcount[hb];
-          if (c == 0 && n > 0) ptx::mbar_wait(o_free, (n - 1) & 1);   // the previous tile's O has been drained
+          if (c == 0 && n > 0) FF_WAIT(prof[5], o_free, (n - 1) & 1);   // the previous tile's O has been drained
           ptx::tc_fence_after();
           const uint32_t hbase = tmem + FF_TM_H + hb * FF_CH;
           for (int j = 0; j < 2; ++j) {
-            ptx::mbar_wait(&w_full[stage], ph);
+            FF_WAIT(prof[6], &w_full[stage], ph);
             ptx::tc_fence_after();
             const uint32_t w_base = ptx::smem_u32(sW + stage * FF_STAGE_BYTES);
 #pragma unroll
@@ -227,7 +249,7 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     for (int t = t_first; t < m_tiles; t += t_step, ++n) {
       for (int c = 0; c < FF_NCH; ++c) {
         const int hb = c & 1;
-        ptx::mbar_wait(&h_full[hb], hcount[hb] & 1);
+        FF_WAIT(prof[7], &h_full[hb], hcount[hb] & 1);
         ++hcount[hb];
         ptx::tc_fence_after();
         const uint32_t haddr = tbase + FF_TM_H + hb * FF_CH + sub * 32;
@@ -248,14 +270,38 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         ptx::tc_fence_before();
         __syncwarp();
         if (lane == 0) ptx::mbar_arrive(&p_full[hb]);
+        if (c == FF_NCH / 2) {                     // pull this thread's residual slice into L2 ahead of the drain
+          const float* xp = X + (size_t)(t * FF_M + q * 32 + lane) * ldx + sub * 64;
+          asm volatile("prefetch.global.L2 [%0];" ::"l"(xp));
+          asm volatile("prefetch.global.L2 [%0];" ::"l"(xp + 32));
+        }
       }
-      // ---- O + b2 + X -> X
-      ptx::mbar_wait(o_full, n & 1);
-      ptx::tc_fence_after();
+      // ---- O + b2 + X -> X.  The residual slice (64 fp32 per thread) is fetched with a two-deep software pipeline
+      // that starts BEFORE the wait on the last GEMM, so its latency overlaps the tail of the tile's MMAs.
       const int row = t * FF_M + q * 32 + lane;
       const int b = __ldg(lay.tile_seq + t);
       const bool valid = __ldg(lay.tile_row0 + t) + q * 32 + lane < __ldg(lay.seq_len + b);
       float* xr = X + (size_t)row * ldx + sub * 64;
+      float res[8][8];
+      auto ld_res = [&](int i) {
+#ifdef FFN_NO_RES
+#pragma unroll
+        for (int e = 0; e < 8; ++e) res[i][e] = 0.f;
+        return;
+#endif
+        asm volatile("ld.global.v8.f32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+                     : "=f"(res[i][0]), "=f"(res[i][1]), "=f"(res[i][2]), "=f"(res[i][3]), "=f"(res[i][4]),
+                       "=f"(res[i][5]), "=f"(res[i][6]), "=f"(res[i][7])
+                     : "l"(xr + i * 8));
+      };
+      ld_res(0);
+      ld_res(1);
+      ld_res(2);
+      FF_WAIT(prof[8], o_full, n & 1);
+      ptx::tc_fence_after();
+#ifdef FFN_PROFILE
+      const long long _td = clock64();
+#endif
 #pragma unroll
       for (int hx = 0; hx < 2; ++hx) {
         float v[32];
@@ -266,25 +312,27 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           if (lane == 0) ptx::mbar_arrive(o_free);
         }
 #pragma unroll
-        for (int i = 0; i < 32; i += 8) {
-          float r[8], bb[8];
-          asm volatile("ld.global.v8.f32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
-                       : "=f"(r[0]), "=f"(r[1]), "=f"(r[2]), "=f"(r[3]), "=f"(r[4]), "=f"(r[5]), "=f"(r[6]), "=f"(r[7])
-                       : "l"(xr + hx * 32 + i));
+        for (int i4 = 0; i4 < 4; ++i4) {
+          const int i = hx * 4 + i4;           // 8-column group of the thread's 64 columns
+          if (i + 3 < 8) ld_res(i + 3);
+          float bb[8];
           asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];"
                        : "=f"(bb[0]), "=f"(bb[1]), "=f"(bb[2]), "=f"(bb[3])
-                       : "r"(sb2_addr + (sub * 64 + hx * 32 + i) * 4));
+                       : "r"(sb2_addr + (sub * 64 + i * 8) * 4));
           asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];"
                        : "=f"(bb[4]), "=f"(bb[5]), "=f"(bb[6]), "=f"(bb[7])
-                       : "r"(sb2_addr + (sub * 64 + hx * 32 + i + 4) * 4));
+                       : "r"(sb2_addr + (sub * 64 + i * 8 + 4) * 4));
           uint32_t o[8];
           float y[8];
 #pragma unroll
           for (int e = 0; e < 8; ++e) {
-            y[e] = valid ? v[i + e] + bb[e] + r[e] : 0.f;
+            y[e] = valid ? v[i4 * 8 + e] + bb[e] + res[i][e] : 0.f;
             o[e] = __float_as_uint(y[e]);
           }
-          asm volatile("st.global.v8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"l"(xr + hx * 32 + i), "r"(o[0]),
+#ifdef FFN_NO_ST
+          if (o[0] == 0x12345678u)
+#endif
+          asm volatile("st.global.v8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"l"(xr + i * 8), "r"(o[0]),
                        "r"(o[1]), "r"(o[2]), "r"(o[3]), "r"(o[4]), "r"(o[5]), "r"(o[6]), "r"(o[7])
                        : "memory");
           if (out1) {
@@ -293,12 +341,21 @@ ffn_fused_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             p4.y = pack_bf16x2(y[2], y[3]);
             p4.z = pack_bf16x2(y[4], y[5]);
             p4.w = pack_bf16x2(y[6], y[7]);
-            *reinterpret_cast<uint4*>(out1 + (size_t)row * ldo1 + sub * 64 + hx * 32 + i) = p4;
+            *reinterpret_cast<uint4*>(out1 + (size_t)row * ldo1 + sub * 64 + i * 8) = p4;
           }
         }
       }
+#ifdef FFN_PROFILE
+      prof[9] += clock64() - _td;
+#endif
     }
   }
+#ifdef FFN_PROFILE
+  if (blockIdx.x == 0 && lane == 0 && (warp < 3))
+    printf("ffn prof warp %d total %lld: w_empty %lld a_free %lld | g1 w_full %lld a_full %lld p_full %lld o_free %lld g2 w_full %lld | "
+           "h_full %lld o_full %lld drain %lld\n", warp, clock64() - t_start, prof[0], prof[1], prof[2], prof[3], prof[4], prof[5],
+           prof[6], prof[7], prof[8], prof[9]);
+#endif
   ptx::tc_fence_before();
   __syncthreads();
   if (warp == 1) ptx::tmem_dealloc(tmem, FF_TM_COLS);
