@@ -237,6 +237,16 @@ def run_ours(args):
     achieved = tc["flops"] / (tc["ms"] * 1e-3) / 1e12
     att = prof.get("attention", dict(launches=0, flops=0, ms=1e-9))
     total_flops = res["hprog"].flops + 10 * be.cfm.estimator.program(res["lay1"].paired()).flops
+    # DRAM bytes per launch of the dominant kernel from the committed ncu capture (profiles/, `ncu --metrics
+    # dram__bytes_read.sum,dram__bytes_write.sum` over the GEMM launches of two estimator calls of this workload)
+    traffic, traffic_src = None, None
+    try:
+        with open(os.path.join(ROOT, "profiles", "r01_dram_traffic_per_launch.json")) as f:
+            tj = json.load(f)["gemm"]
+        traffic = tj["dram_read_bytes_per_launch"] + tj["dram_write_bytes_per_launch"]
+        traffic_src = "profiles/r01_dram_traffic_per_launch.json (ncu, mean over %d launches)" % tj["launches"]
+    except Exception:
+        pass
     out = {
         "metric": "audio_seconds_per_second", "value": world * audio_seconds(B) / (ms_step * 1e-3), "unit": "audio-s/s",
         "n_gpus": world, "steps": K, "warmup": W, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
@@ -251,7 +261,8 @@ def run_ours(args):
         "clocks": clocks,
         "roofline": {"bound": "tensor", "kernel": "tapgemm_tc_kernel (tcgen05 implicit-GEMM conv/linear)",
                      "achieved": achieved, "peak": pk["tflops"], "unit": "TFLOP/s", "frac": achieved / pk["tflops"],
-                     "peak_source": pk["src"] + " bf16_tflops_sustained", "traffic": None,
+                     "peak_source": pk["src"] + " bf16_tflops_sustained", "traffic": traffic, "traffic_source": traffic_src,
+                     "hbm_gbps_from_traffic": (traffic * tc["launches"] / (tc["ms"] * 1e-3) / 1e9) if traffic else None,
                      "launches_per_step": tc["launches"], "kernel_ms_per_step": tc["ms"],
                      "share_of_eager_step": tc["ms"] / prof["_step_ms_eager"],
                      "attention": {"kernel": "attention_tc_kernel (tcgen05/TMEM flash)", "launches": att["launches"],
