@@ -3,8 +3,8 @@
 // Reference: cosyvoice/flow/components/transformer.py:266-271 -> diffusers Attention / AttnProcessor2_0
 // (F.scaled_dot_product_attention with the all-ones additive mask of flow/decoder.py:258 = no mask at B=1).
 //
-// One CTA per (128-query tile, head); 2 CTAs co-resident per SM (256 TMEM columns, 80 KiB smem each) so that one
-// CTA's softmax overlaps the other's MMAs.
+// Work item = (128-query tile, head), items strided over a persistent grid; 2 CTAs co-resident per SM (256 TMEM
+// columns, 80 KiB smem each) so that one CTA's softmax overlaps the other's MMAs.
 //   warp 0      : TMA producer -- Q tile once, then (K, V) 128-key tiles into a 2-stage ring; Q, K and V are
 //                 128x64 boxes of the SAME time-major qkv buffer (one tensor map, 128B swizzle).
 //   warp 1      : TMEM allocator + single-thread tcgen05.mma issuer
@@ -24,13 +24,14 @@
 namespace cvb {
 
 using Layout = cvb200_layout;
+int device_sm_count();        // tapgemm_tc.cu
 
 namespace {
 
 constexpr int HD = 64, BQ = 128, BK = 128;
 constexpr int TILE_BYTES = 128 * 64 * 2;            // 16 KiB
 constexpr int KV_STAGES = 2;
-constexpr int SMEM_BYTES = 1024 + TILE_BYTES * (1 + 2 * KV_STAGES) + 128 + 2 * 2 * 128 * 4;
+constexpr int SMEM_BYTES = 1024 + TILE_BYTES * (1 + 2 * KV_STAGES) + 128 + 2 * 2 * 128 * 4;   // barriers + smax
 constexpr int TM_S = 0, TM_P = 128, TM_O = 192, TM_COLS = 256;
 
 // MN-major 128B-swizzled shared-memory operand (V tile: rows = keys (K dim), 64 d (N dim) contiguous = 128 B).
@@ -56,16 +57,30 @@ __device__ __forceinline__ uint32_t pack2(float lo, float hi) {
   return *reinterpret_cast<uint32_t*>(&t);
 }
 
+// Work item = (128-query tile, head), items strided over a persistent grid of 2 CTAs per SM: barriers, TMEM and the
+// tensor map are set up once per CTA, and the K/V ring keeps streaming across item boundaries (at T = 609 an item is
+// only 5 key blocks, so a per-item prologue was a quarter of its time).  All block-level barrier parities run on a
+// global block counter g; q_full / q_free / o_free run on the item counter n.
+struct AttnItem {
+  int head, b, q0, len, seq0, nblk;
+  bool valid;
+};
+__device__ __forceinline__ AttnItem attn_item(const Layout& lay, int it, int heads) {
+  AttnItem w;
+  w.head = it % heads;
+  const int tile = it / heads;
+  w.b = __ldg(lay.tile_seq + tile);
+  w.q0 = __ldg(lay.tile_row0 + tile);
+  w.len = __ldg(lay.seq_len + w.b);
+  w.seq0 = __ldg(lay.seq_row0 + w.b);
+  w.nblk = (w.len + BK - 1) / BK;
+  w.valid = w.q0 < w.len;                                  // padding-only tiles are skipped by every role
+  return w;
+}
+
 __global__ void __launch_bounds__(320, 2)
 attention_tc_kernel(const __grid_constant__ CUtensorMap tm, __nv_bfloat16* __restrict__ out, int ldo, const Layout lay,
-                    int heads, float scale_log2) {
-  const int head = blockIdx.x % heads, tile = blockIdx.x / heads;
-  const int b = __ldg(lay.tile_seq + tile);
-  const int q0 = __ldg(lay.tile_row0 + tile);
-  const int len = __ldg(lay.seq_len + b);
-  if (q0 >= len) return;                                   // padding-only tile (uniform for the CTA)
-  const int seq0 = __ldg(lay.seq_row0 + b);
-  const int nblk = (len + BK - 1) / BK;
+                    int heads, float scale_log2, int n_items) {
   const int inner = heads * HD;
 
   extern __shared__ uint8_t smem_raw[];
@@ -81,8 +96,10 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tm, __nv_bfloat16* __res
   uint64_t* s_free = bars + 6;
   uint64_t* p_full = bars + 7;
   uint64_t* pv_done = bars + 8;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 9);
-  float* smax = reinterpret_cast<float*>(bars + 10);      // [2 parities][2 halves][128 rows]
+  uint64_t* q_free = bars + 9;                             // every QK^T of the item has retired: Q may be overwritten
+  uint64_t* o_free = bars + 10;                            // the item's O has been read out (256 arrivals)
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 11);
+  float* smax = reinterpret_cast<float*>(bars + 12);      // [2 parities][2 halves][128 rows]
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   if (threadIdx.x == 0) {
@@ -92,6 +109,8 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tm, __nv_bfloat16* __res
     ptx::mbar_init(s_free, 256);
     ptx::mbar_init(p_full, 256);
     ptx::mbar_init(pv_done, 1);
+    ptx::mbar_init(q_free, 1);
+    ptx::mbar_init(o_free, 256);
     ptx::fence_barrier_init();
     ptx::prefetch_tensormap(&tm);
   }
@@ -105,14 +124,21 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tm, __nv_bfloat16* __res
 
   if (warp == 0) {
     if (lane == 0) {
-      ptx::mbar_arrive_expect_tx(q_full, TILE_BYTES);
-      ptx::tma_load_2d(sQ, &tm, q_full, head * HD, seq0 + q0);
-      for (int j = 0; j < nblk; ++j) {
-        const int st = j % KV_STAGES;
-        ptx::mbar_wait(&kv_empty[st], ((j / KV_STAGES) & 1) ^ 1);
-        ptx::mbar_arrive_expect_tx(&kv_full[st], 2 * TILE_BYTES);
-        ptx::tma_load_2d(sK + st * TILE_BYTES, &tm, &kv_full[st], inner + head * HD, seq0 + j * BK);
-        ptx::tma_load_2d(sV + st * TILE_BYTES, &tm, &kv_full[st], 2 * inner + head * HD, seq0 + j * BK);
+      uint32_t n = 0, g = 0;
+      for (int it = blockIdx.x; it < n_items; it += gridDim.x) {
+        const AttnItem w = attn_item(lay, it, heads);
+        if (!w.valid) continue;
+        if (n > 0) ptx::mbar_wait(q_free, (n - 1) & 1);
+        ptx::mbar_arrive_expect_tx(q_full, TILE_BYTES);
+        ptx::tma_load_2d(sQ, &tm, q_full, w.head * HD, w.seq0 + w.q0);
+        for (int j = 0; j < w.nblk; ++j, ++g) {
+          const int st = g % KV_STAGES;
+          ptx::mbar_wait(&kv_empty[st], ((g / KV_STAGES) & 1) ^ 1);
+          ptx::mbar_arrive_expect_tx(&kv_full[st], 2 * TILE_BYTES);
+          ptx::tma_load_2d(sK + st * TILE_BYTES, &tm, &kv_full[st], inner + w.head * HD, w.seq0 + j * BK);
+          ptx::tma_load_2d(sV + st * TILE_BYTES, &tm, &kv_full[st], 2 * inner + w.head * HD, w.seq0 + j * BK);
+        }
+        ++n;
       }
     }
   } else if (warp == 1) {
@@ -120,11 +146,10 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tm, __nv_bfloat16* __res
       const uint32_t idesc_qk = ptx::make_idesc_bf16(BQ, BK);                       // 128 x 128, A/B K-major
       const uint32_t idesc_pv = ptx::make_idesc_bf16(BQ, HD) | (1u << 16);          // 128 x 64, B MN-major
       const uint32_t q_base = ptx::smem_u32(sQ);
-      ptx::mbar_wait(q_full, 0);
-      auto issue_qk = [&](int j) {
-        const int st = j % KV_STAGES;
-        ptx::mbar_wait(&kv_full[st], (j / KV_STAGES) & 1);
-        if (j > 0) ptx::mbar_wait(s_free, (j - 1) & 1);       // softmax has pulled S(j-1) out of TMEM
+      auto issue_qk = [&](uint32_t gg) {
+        const int st = gg % KV_STAGES;
+        ptx::mbar_wait(&kv_full[st], (gg / KV_STAGES) & 1);
+        if (gg > 0) ptx::mbar_wait(s_free, (gg - 1) & 1);     // softmax has pulled S(g-1) out of TMEM
         ptx::tc_fence_after();
         const uint32_t k_base = ptx::smem_u32(sK + st * TILE_BYTES);
 #pragma unroll
@@ -133,18 +158,27 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tm, __nv_bfloat16* __res
                        idesc_qk, k != 0);
         ptx::umma_commit(s_full);
       };
-      issue_qk(0);
-      for (int j = 0; j < nblk; ++j) {
-        if (j + 1 < nblk) issue_qk(j + 1);
-        const int st = j % KV_STAGES;
-        ptx::mbar_wait(p_full, j & 1);                        // P(j) is in TMEM, O has been rescaled
-        ptx::tc_fence_after();
-        const uint32_t v_base = ptx::smem_u32(sV + st * TILE_BYTES);
+      uint32_t n = 0, g = 0;
+      for (int it = blockIdx.x; it < n_items; it += gridDim.x) {
+        const AttnItem w = attn_item(lay, it, heads);
+        if (!w.valid) continue;
+        ptx::mbar_wait(q_full, n & 1);
+        issue_qk(g);
+        for (int j = 0; j < w.nblk; ++j, ++g) {
+          if (j + 1 < w.nblk) issue_qk(g + 1);
+          else ptx::umma_commit(q_free);                       // the item's last QK^T is in flight
+          const int st = g % KV_STAGES;
+          ptx::mbar_wait(p_full, g & 1);                       // P(g) is in TMEM, O has been rescaled
+          if (j == 0 && n > 0) ptx::mbar_wait(o_free, (n - 1) & 1);   // previous item's O has been read out
+          ptx::tc_fence_after();
+          const uint32_t v_base = ptx::smem_u32(sV + st * TILE_BYTES);
 #pragma unroll
-        for (int k = 0; k < BK / 16; ++k)
-          ptx::umma_ts(tmem + TM_O, tmem + TM_P + k * 8, make_sw128_mnmajor_desc(v_base + k * 2048), idesc_pv, (j | k) != 0);
-        ptx::umma_commit(&kv_empty[st]);
-        ptx::umma_commit(pv_done);
+          for (int k = 0; k < BK / 16; ++k)
+            ptx::umma_ts(tmem + TM_O, tmem + TM_P + k * 8, make_sw128_mnmajor_desc(v_base + k * 2048), idesc_pv, (j | k) != 0);
+          ptx::umma_commit(&kv_empty[st]);
+          ptx::umma_commit(pv_done);
+        }
+        ++n;
       }
     }
   } else {
@@ -156,90 +190,98 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tm, __nv_bfloat16* __res
     const int half = (warp - 2) >> 2;
     const int row = lane_grp * 32 + lane;
     const uint32_t tbase = tmem + ((uint32_t)(lane_grp * 32) << 16);
-    float m_run = -INFINITY, l_half = 0.f;
-    for (int j = 0; j < nblk; ++j) {
-      ptx::mbar_wait(s_full, j & 1);
-      ptx::tc_fence_after();
-      const int nvalid = len - j * BK - half * 64;            // valid keys among this thread's 64 columns
-      uint32_t raw[2][32];
-      ptx::tmem_ld32_nowait(tbase + TM_S + half * 64, raw[0]);
-      ptx::tmem_ld32_nowait(tbase + TM_S + half * 64 + 32, raw[1]);
-      ptx::tmem_wait_ld();
-      ptx::tc_fence_before();
-      ptx::mbar_arrive(s_free);                               // S(j) is in registers: QK(j+1) may overwrite it
-      float v[64];
+    uint32_t g = 0;
+    for (int it = blockIdx.x; it < n_items; it += gridDim.x) {
+      const AttnItem w = attn_item(lay, it, heads);
+      if (!w.valid) continue;
+      const int len = w.len;
+      float m_run = -INFINITY, l_half = 0.f;
+      for (int j = 0; j < w.nblk; ++j, ++g) {
+        ptx::mbar_wait(s_full, g & 1);
+        ptx::tc_fence_after();
+        const int nvalid = len - j * BK - half * 64;            // valid keys among this thread's 64 columns
+        uint32_t raw[2][32];
+        ptx::tmem_ld32_nowait(tbase + TM_S + half * 64, raw[0]);
+        ptx::tmem_ld32_nowait(tbase + TM_S + half * 64 + 32, raw[1]);
+        ptx::tmem_wait_ld();
+        ptx::tc_fence_before();
+        ptx::mbar_arrive(s_free);                               // S(g) is in registers: QK(g+1) may overwrite it
+        float v[64];
 #pragma unroll
-      for (int i = 0; i < 64; ++i) v[i] = __uint_as_float(raw[i >> 5][i & 31]);
-      if (nvalid < 64) {
+        for (int i = 0; i < 64; ++i) v[i] = __uint_as_float(raw[i >> 5][i & 31]);
+        if (nvalid < 64) {
 #pragma unroll
-        for (int i = 0; i < 64; ++i) if (i >= nvalid) v[i] = -INFINITY;
-      }
-      float mx4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
-#pragma unroll
-      for (int i = 0; i < 64; i += 4) {
-        mx4[0] = fmaxf(mx4[0], v[i]);
-        mx4[1] = fmaxf(mx4[1], v[i + 1]);
-        mx4[2] = fmaxf(mx4[2], v[i + 2]);
-        mx4[3] = fmaxf(mx4[3], v[i + 3]);
-      }
-      const float m_loc = fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3]));
-      float* xch = smax + (j & 1) * 256;
-      xch[half * 128 + row] = m_loc;
-      ptx::named_bar_sync(1, 256);
-      const float m_new = fmaxf(m_run, fmaxf(m_loc, xch[(half ^ 1) * 128 + row]));
-      const float corr = ex2_approx((m_run - m_new) * scale_log2);   // first block: exp2(-inf) = 0
-      const bool moved = __any_sync(0xffffffffu, m_new > m_run);
-      m_run = m_new;
-      const float moff = m_new * scale_log2;
-      if (j > 0) ptx::mbar_wait(pv_done, (j - 1) & 1);               // PV(j-1) retired: P and O may be touched
-      ptx::tc_fence_after();
-      float ls4[4] = {0.f, 0.f, 0.f, 0.f};
-#pragma unroll
-      for (int c = 0; c < 64; c += 32) {
-        uint32_t pk[16];
-#pragma unroll
-        for (int i = 0; i < 32; i += 2) {
-          const float p0 = ex2_approx(fmaf(v[c + i], scale_log2, -moff));       // masked columns: exp2(-inf) = 0
-          const float p1 = ex2_approx(fmaf(v[c + i + 1], scale_log2, -moff));
-          ls4[(i >> 1) & 3] += p0 + p1;
-          pk[i >> 1] = pack2(p0, p1);
+          for (int i = 0; i < 64; ++i) if (i >= nvalid) v[i] = -INFINITY;
         }
-        ptx::tmem_st16(tbase + TM_P + half * 32 + (c >> 1), pk);
-      }
-      l_half = l_half * corr + ((ls4[0] + ls4[1]) + (ls4[2] + ls4[3]));
-      if (j > 0 && moved) {                                          // rescale this thread's 32 output columns
-        float o[32];
-        ptx::tmem_ld32(tbase + TM_O + half * 32, o);
-        uint32_t lo[16], hi[16];
+        float mx4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
 #pragma unroll
-        for (int i = 0; i < 16; ++i) { lo[i] = __float_as_uint(o[i] * corr); hi[i] = __float_as_uint(o[16 + i] * corr); }
-        ptx::tmem_st16(tbase + TM_O + half * 32, lo);
-        ptx::tmem_st16(tbase + TM_O + half * 32 + 16, hi);
+        for (int i = 0; i < 64; i += 4) {
+          mx4[0] = fmaxf(mx4[0], v[i]);
+          mx4[1] = fmaxf(mx4[1], v[i + 1]);
+          mx4[2] = fmaxf(mx4[2], v[i + 2]);
+          mx4[3] = fmaxf(mx4[3], v[i + 3]);
+        }
+        const float m_loc = fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3]));
+        float* xch = smax + (g & 1) * 256;
+        xch[half * 128 + row] = m_loc;
+        ptx::named_bar_sync(1, 256);
+        const float m_new = fmaxf(m_run, fmaxf(m_loc, xch[(half ^ 1) * 128 + row]));
+        const float corr = ex2_approx((m_run - m_new) * scale_log2);   // first block: exp2(-inf) = 0
+        const bool moved = __any_sync(0xffffffffu, m_new > m_run);
+        m_run = m_new;
+        const float moff = m_new * scale_log2;
+        if (g > 0) ptx::mbar_wait(pv_done, (g - 1) & 1);               // PV(g-1) retired: P and O may be touched
+        ptx::tc_fence_after();
+        float ls4[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+        for (int c = 0; c < 64; c += 32) {
+          uint32_t pk[16];
+#pragma unroll
+          for (int i = 0; i < 32; i += 2) {
+            const float p0 = ex2_approx(fmaf(v[c + i], scale_log2, -moff));       // masked columns: exp2(-inf) = 0
+            const float p1 = ex2_approx(fmaf(v[c + i + 1], scale_log2, -moff));
+            ls4[(i >> 1) & 3] += p0 + p1;
+            pk[i >> 1] = pack2(p0, p1);
+          }
+          ptx::tmem_st16(tbase + TM_P + half * 32 + (c >> 1), pk);
+        }
+        l_half = l_half * corr + ((ls4[0] + ls4[1]) + (ls4[2] + ls4[3]));
+        if (j > 0 && moved) {                                          // rescale this thread's 32 output columns
+          float o[32];
+          ptx::tmem_ld32(tbase + TM_O + half * 32, o);
+          uint32_t lo[16], hi[16];
+#pragma unroll
+          for (int i = 0; i < 16; ++i) { lo[i] = __float_as_uint(o[i] * corr); hi[i] = __float_as_uint(o[16 + i] * corr); }
+          ptx::tmem_st16(tbase + TM_O + half * 32, lo);
+          ptx::tmem_st16(tbase + TM_O + half * 32 + 16, hi);
+        }
+        ptx::tmem_wait_st();
+        ptx::tc_fence_before();
+        ptx::mbar_arrive(p_full);
       }
-      ptx::tmem_wait_st();
+      // ---- epilogue: O / l -> bf16 (each thread writes 32 of the row's 64 output columns)
+      float* xch = smax + (g & 1) * 256;
+      xch[half * 128 + row] = l_half;
+      ptx::named_bar_sync(1, 256);
+      const float inv = 1.f / (l_half + xch[(half ^ 1) * 128 + row]);
+      ptx::mbar_wait(pv_done, (g - 1) & 1);
+      ptx::tc_fence_after();
+      const int lrow = w.q0 + row;
+      float o[32];
+      ptx::tmem_ld32(tbase + TM_O + half * 32, o);
       ptx::tc_fence_before();
-      ptx::mbar_arrive(p_full);
-    }
-    // ---- epilogue: O / l -> bf16 (each thread writes 32 of the row's 64 output columns)
-    float* xch = smax + (nblk & 1) * 256;
-    xch[half * 128 + row] = l_half;
-    ptx::named_bar_sync(1, 256);
-    const float inv = 1.f / (l_half + xch[(half ^ 1) * 128 + row]);
-    ptx::mbar_wait(pv_done, (nblk - 1) & 1);
-    ptx::tc_fence_after();
-    const int lrow = q0 + row;
-    float o[32];
-    ptx::tmem_ld32(tbase + TM_O + half * 32, o);
-    if (lrow < len) {
-      __nv_bfloat16* dst = out + (size_t)(seq0 + lrow) * ldo + head * HD + half * 32;
+      ptx::mbar_arrive(o_free);                                        // the next item's first PV may overwrite O
+      if (lrow < len) {
+        __nv_bfloat16* dst = out + (size_t)(w.seq0 + lrow) * ldo + w.head * HD + half * 32;
 #pragma unroll
-      for (int i = 0; i < 32; i += 8) {
-        uint4 pk;
-        pk.x = pack2(o[i] * inv, o[i + 1] * inv);
-        pk.y = pack2(o[i + 2] * inv, o[i + 3] * inv);
-        pk.z = pack2(o[i + 4] * inv, o[i + 5] * inv);
-        pk.w = pack2(o[i + 6] * inv, o[i + 7] * inv);
-        *reinterpret_cast<uint4*>(dst + i) = pk;
+        for (int i = 0; i < 32; i += 8) {
+          uint4 pk;
+          pk.x = pack2(o[i] * inv, o[i + 1] * inv);
+          pk.y = pack2(o[i + 2] * inv, o[i + 3] * inv);
+          pk.z = pack2(o[i + 4] * inv, o[i + 5] * inv);
+          pk.w = pack2(o[i + 6] * inv, o[i + 7] * inv);
+          *reinterpret_cast<uint4*>(dst + i) = pk;
+        }
       }
     }
   }
@@ -293,9 +335,11 @@ int launch_attention_tc(const void* qkv, int ld, void* out, int ldo, const Layou
     attr_err = cudaFuncSetAttribute(attention_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
   });
   CVB_CUDA(attr_err);
-  const int grid = (lay.rows / 128) * heads;
-  CVB_CUDA(launch_pdl(attention_tc_kernel, dim3(grid), dim3(320), SMEM_BYTES, st, tm, reinterpret_cast<__nv_bfloat16*>(out), ldo, lay, heads,
-                                                     scale * 1.4426950408889634f));
+  const int n_items = (lay.rows / 128) * heads;
+  const int slots = 2 * device_sm_count();                 // 2 co-resident CTAs per SM
+  const int grid = n_items < slots ? n_items : slots;
+  CVB_CUDA(launch_pdl(attention_tc_kernel, dim3(grid), dim3(320), SMEM_BYTES, st, tm, reinterpret_cast<__nv_bfloat16*>(out), ldo,
+                      lay, heads, scale * 1.4426950408889634f, n_items));
   CVB_LAUNCH_CHECK();
   return CVB_OK;
 }

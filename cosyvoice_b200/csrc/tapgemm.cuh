@@ -106,6 +106,9 @@ template <int NV> __device__ __forceinline__ void vec_add_dt(const void* base, s
 }
 // 256-bit global store (sm_100+): one full 32-byte sector per thread per instruction
 __device__ __forceinline__ void st_global_v8(void* p, const uint32_t (&r)[8]) {
+#ifdef CVB_EXPERIMENT_NO_STORE
+  if (r[0] != 0x7fc12345u) return;       // experiment: how much of the kernel is the store path
+#endif
   asm volatile("st.global.v8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"l"(p), "r"(r[0]), "r"(r[1]), "r"(r[2]),
                "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7])
                : "memory");
