@@ -47,6 +47,7 @@ int launch_snake(const void*, int, int, void*, int, int, const float*, int, cons
 int launch_reflect_row0(void*, int, int, int, const Layout&, cudaStream_t);
 int launch_ffn_fused(const void*, int, const void*, const float*, const void*, const float*, float*, int, void*, int,
                      const cvb200_layout&, cudaStream_t);
+int launch_split3_bf16(const float*, int, int, int, void*, int, long long, cudaStream_t);
 int launch_anti_alias_rows(const void*, int, int, void*, int, int, const float*, const float*, const float*, int,
                            const Layout&, cudaStream_t);
 int launch_anti_alias_nct(const void*, void*, int, int, int, int, const float*, const float*, const float*, const float*,
@@ -93,6 +94,10 @@ int cvb200_ffn_fused(const void* a, int lda, const void* w1, const float* b1, co
                      int ldx, void* out1, int ldo1, const cvb200_layout* lay, void* stream) {
   CVB_REQUIRE(lay != nullptr, "null layout");
   return launch_ffn_fused(a, lda, w1, b1, w2, b2, x, ldx, out1, ldo1, *lay, ST(stream));
+}
+
+int cvb200_split3_bf16(const float* x, int ldx, int C, int cpad, void* out, int ldo, int64_t rows, void* stream) {
+  return launch_split3_bf16(x, ldx, C, cpad, out, ldo, (long long)rows, ST(stream));
 }
 
 int cvb200_layernorm(const float* x, int ldx, void* out, int ldo, int out_dt, const float* gamma, const float* beta,

@@ -224,6 +224,29 @@ __global__ void __launch_bounds__(256) euler_cfg_kernel(float* __restrict__ x, c
   reinterpret_cast<float4*>(x)[i] = xv;
 }
 
+// ---------------------------------------------------------------------------- fp32 -> 3 x bf16 split
+// x = x1 + x2 + x3 with x1 = bf16(x), x2 = bf16(x - x1), x3 = bf16(x - x1 - x2): 24 mantissa bits in three bf16
+// operands, so that a product with 16-24 bit operand mantissas runs on the bf16 tensor cores (hift.py f0 path).
+// out[row, i*cpad + c] = x_i[row, c]; columns c >= C of each block are written as zeros.
+__global__ void __launch_bounds__(256) split3_bf16_kernel(const float* __restrict__ x, int ldx, int C, int cpad,
+                                                          __nv_bfloat16* __restrict__ out, int ldo, long long total) {
+  pdl_sync();
+  const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= total) return;
+  const int c = (int)(idx % cpad);
+  const long long row = idx / cpad;
+  float v = c < C ? x[row * ldx + c] : 0.f;
+  const __nv_bfloat16 h1 = __float2bfloat16_rn(v);
+  v -= __bfloat162float(h1);
+  const __nv_bfloat16 h2 = __float2bfloat16_rn(v);
+  v -= __bfloat162float(h2);
+  const __nv_bfloat16 h3 = __float2bfloat16_rn(v);
+  __nv_bfloat16* o = out + row * ldo + c;
+  o[0] = h1;
+  o[cpad] = h2;
+  o[2 * cpad] = h3;
+}
+
 // ---------------------------------------------------------------------------- layout transposes
 // [B, C, T] (fp32) -> time-major rows.  32x32 smem tile transpose; grid (row tiles of 32, C tiles of 32).
 __global__ void __launch_bounds__(256) nct_to_rows_kernel(const float* __restrict__ src, long long seq_stride,
@@ -325,6 +348,16 @@ int launch_euler_cfg(float* x, const float* v, long long n_half, float dt, float
   const long long n4 = n_half / 4;
   if (n4 <= 0) return CVB_OK;
   CVB_CUDA(launch_pdl(euler_cfg_kernel, dim3((unsigned)((n4 + 255) / 256)), dim3(256), 0, st, x, v, n4, dt, cfg));
+  CVB_LAUNCH_CHECK();
+  return CVB_OK;
+}
+
+int launch_split3_bf16(const float* x, int ldx, int C, int cpad, void* out, int ldo, long long rows, cudaStream_t st) {
+  CVB_REQUIRE(x && out && C > 0 && cpad >= C && ldo >= 3 * cpad, "split3: bad shapes");
+  const long long total = rows * cpad;
+  if (total <= 0) return CVB_OK;
+  CVB_CUDA(launch_pdl(split3_bf16_kernel, dim3((unsigned)((total + 255) / 256)), dim3(256), 0, st, x, ldx, C, cpad,
+                      reinterpret_cast<__nv_bfloat16*>(out), ldo, total));
   CVB_LAUNCH_CHECK();
   return CVB_OK;
 }

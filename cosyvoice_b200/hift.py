@@ -7,6 +7,7 @@ transposed conv is an instance of the tap GEMM; Snake / LeakyReLU / residual / 1
 fusion ride in its epilogue; the sine source, STFT and the exp-sin-iSTFT-OLA head are single kernels.
 """
 import math
+import os
 from typing import Dict, List, Optional, Sequence, Tuple
 
 import numpy as np
@@ -44,6 +45,27 @@ class _ResBlockW:
             self.alpha2.append(f32(f"{p}activations2.{i}.alpha"))
 
 
+def _split3_conv_plan(w: torch.Tensor, bias, device, cpad: int):
+    """'same' Conv1d [N, C, k] on the bf16 split of its fp32 input ([rows, 3*cpad], ops.split3_bf16) with the same split
+    of its weights: atoms (tap shift, term column block, weight term) for the cross terms of lowest order."""
+    from .packing import build_plan
+    w = w.detach().float()
+    N, Cin, k = w.shape
+    w1 = w.to(torch.bfloat16).float()
+    w2 = (w - w1).to(torch.bfloat16).float()
+    w3 = (w - w1 - w2).to(torch.bfloat16).float()
+    terms = (w1, w2, w3)
+    atoms = []
+    for j in range(k):
+        q = j - (k - 1) // 2
+        pairs = ((0, 0), (0, 1), (1, 0), (0, 2), (1, 1), (2, 0))
+        if os.environ.get("CVB200_F0_TERMS", "3") != "6":
+            pairs = pairs[:3]
+        for i, kk in pairs:
+            atoms.append((q, i * cpad, terms[kk][:, :, j]))
+    return build_plan([atoms], N, cpad, bias, torch.bfloat16, device)
+
+
 class _Weights:
     def __init__(self, sd: SD, v2: bool, dtype, device):
         a = _arch(v2)
@@ -51,13 +73,23 @@ class _Weights:
         self.rates, self.ks = a["rates"], a["ks"]
         f32 = lambda key: sd[key].detach().float().to(device).contiguous()
         self.hop = int(np.prod(self.rates)) * HOP
-        # f0 predictor always runs in fp32: its output is integrated over the whole utterance by the
-        # sine source (generator.py:148), so operand rounding would show up as audible phase drift.
-        self.f0_convs = []
+        # The f0 predictor never runs on plain bf16 operands: its output is integrated over the whole utterance by
+        # the sine source (generator.py:148), so operand rounding would show up as audible phase drift.
+        #   fp32 engine: CUDA-core tap GEMM (parity mode).
+        #   bf16 engine: activations and weights are split into bf16 terms (x = x1 + x2 [+ x3], ops.split3_bf16) and
+        #   ONE tcgen05 tap GEMM sums the cross terms x1w1 + x1w2 + x2w1 in its fp32 accumulator (16-bit operand
+        #   mantissas).  Measured f0 error against the fp32 engine: 3e-5 relative (tests/test_gpu_hift.py); the
+        #   24-bit six-term variant (CVB200_F0_TERMS=6) measures 5e-5, i.e. the tensor core's accumulator rounding,
+        #   not the operands, is what is left.  3x the MMA work of a bf16 conv, ~10x faster than the CUDA-core path
+        #   (which was 3 % of the bench step).
+        self.f0_convs, self.f0_split_convs = [], []
         cpad = 128
         for i in range(5):
             p = f"f0_predictor.condnet.{2 * i}."
-            self.f0_convs.append(conv1d_plan(fold_weight_norm(sd, p), sd[p + "bias"], torch.float32, device, c_pad=cpad))
+            w_f0 = fold_weight_norm(sd, p)
+            self.f0_convs.append(conv1d_plan(w_f0, sd[p + "bias"], torch.float32, device, c_pad=cpad))
+            if dtype == torch.bfloat16:
+                self.f0_split_convs.append(_split3_conv_plan(w_f0, sd[p + "bias"], device, cpad))
             cpad = 512
         self.f0_w = f32("f0_predictor.classifier.weight").reshape(-1)
         self.f0_b = f32("f0_predictor.classifier.bias").reshape(-1)
@@ -130,14 +162,29 @@ class _Program:
         self.flops = 0
         simt = _lib.ENGINE_SIMT
 
-        # ---- f0 predictor (fp32, CUDA cores): 5 x (conv k3 + ELU), Linear 512->1, abs
+        # ---- f0 predictor: 5 x (conv k3 + ELU), Linear 512->1, abs (fp32 accuracy on either engine, see _Weights)
         self.ops_f0: List[ops.Op] = []
-        src, dst = self.mel32, self.fa
-        for i, plan in enumerate(w.f0_convs):
-            fl = plan.flops_per_row * sum(lay0.lens)
-            self.ops_f0.append(ops.gemm_op(plan, src, lay0, dst, engine=simt, act=_lib.ACT_ELU, flops=fl))
-            self.flops += fl
-            src, dst = dst, (self.fb if dst is self.fa else self.fa)
+        if w.f0_split_convs and engine == _lib.ENGINE_TCGEN05:
+            self.msplit = z(R0, 3 * 128)
+            self.hsplit = z(R0, 3 * 512)
+            self.ops_f0.append(lambda: ops.split3_bf16(self.mel32, self.msplit, 80, 128))
+            a_in = self.msplit
+            for i, (plan, plan32) in enumerate(zip(w.f0_split_convs, w.f0_convs)):
+                fl = plan32.flops_per_row * sum(lay0.lens)          # algorithmic FLOPs of the conv, not of the 6 terms
+                self.ops_f0.append(ops.gemm_op(plan, a_in, lay0, self.fa, engine=_lib.ENGINE_TCGEN05, act=_lib.ACT_ELU,
+                                               flops=fl))
+                self.flops += fl
+                if i + 1 < len(w.f0_split_convs):
+                    self.ops_f0.append(lambda: ops.split3_bf16(self.fa, self.hsplit, 512, 512))
+                a_in = self.hsplit
+            src = self.fa
+        else:
+            src, dst = self.mel32, self.fa
+            for i, plan in enumerate(w.f0_convs):
+                fl = plan.flops_per_row * sum(lay0.lens)
+                self.ops_f0.append(ops.gemm_op(plan, src, lay0, dst, engine=simt, act=_lib.ACT_ELU, flops=fl))
+                self.flops += fl
+                src, dst = dst, (self.fb if dst is self.fa else self.fa)
         f0_in = src
         self.ops_f0.append(lambda: ops.rowdot_abs(f0_in, w.f0_w, w.f0_b, self.f0, R0))
         # ---- source: f0 -> s (generator.py:404-406)

@@ -223,6 +223,14 @@ def istft16(x, lay: SeqLayout, wav, limit: float):
                                           _stream()), "istft16")
 
 
+def split3_bf16(x: torch.Tensor, out: torch.Tensor, C_: int, cpad: int):
+    """x fp32 [rows, >=C] -> out bf16 [rows, 3*cpad]: three bf16 terms whose sum is x to 24 bits."""
+    _require_cuda(x, out)
+    assert x.dtype == torch.float32 and out.dtype == torch.bfloat16
+    _lib.check(_lib.load().cvb200_split3_bf16(x.data_ptr(), x.stride(0), C_, cpad, out.data_ptr(), out.stride(0),
+                                              x.shape[0], _stream()), "split3_bf16")
+
+
 def snake(x, out, alpha, C_: int, lay: SeqLayout):
     _require_cuda(x, out)
     _lib.check(_lib.load().cvb200_snake(x.data_ptr(), x.stride(0), dt_of(x), out.data_ptr(), out.stride(0), dt_of(out),

@@ -144,6 +144,11 @@ int cvb200_tapgemm(const cvb200_gemm* p, int engine, void* stream);
 int cvb200_ffn_fused(const void* a, int lda, const void* w1, const float* b1, const void* w2, const float* b2, float* x,
                      int ldx, void* out1, int ldo1, const cvb200_layout* lay, void* stream);
 
+/* fp32 -> three bf16 operands with x = x1 + x2 + x3 (24 mantissa bits): out[row, i*cpad + c] = x_i[row, c], i = 0..2.
+ * Lets the f0 predictor (cosyvoice/hifigan/f0_predictor.py:52-55, whose output is integrated into the source phase)
+ * run on the bf16 tensor cores with split operands: one tap GEMM over the cross terms x_i * w_k of lowest order. */
+int cvb200_split3_bf16(const float* x, int ldx, int C, int cpad, void* out, int ldo, int64_t rows, void* stream);
+
 /* LayerNorm(256) over channels of each row: flow/components/transformer.py:195,231,262,300 */
 int cvb200_layernorm(const float* x, int ldx, void* out, int ldo, int out_dt, const float* gamma,
                      const float* beta, int rows, int C, float eps, void* stream);

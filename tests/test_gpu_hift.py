@@ -207,3 +207,30 @@ def test_hift_program_rebinds_lengths(golden_dir, ver):
     wavs, ss = gen.inference_batch([d["mel"]], phase_vec=d["phase_vec"], noise=d["noise"])
     assert (ss[0].cpu() - d["s"]).abs().max().item() < 3e-4
     assert (wavs[0].cpu() - d["wav"]).abs().max().item() < 2e-3
+
+
+@pytest.mark.parametrize("ver", ["v1", "v2"])
+def test_f0_on_tensor_cores_keeps_fp32_accuracy(golden_dir, ver):
+    """bf16 engine: the f0 predictor runs on split bf16 operands (activations and weights, cross terms summed in one
+    tcgen05 tap GEMM).  Stated bound: f0 within 1e-4 relative of the fp32 CUDA-core engine and of the reference's f0
+    (measured 3e-5; plain bf16 operands would be ~1e-2): f0 is integrated into the source phase."""
+    d = _load(golden_dir, f"hift_{ver}.pt")
+    T = d["mel"].shape[-1]
+    g = torch.Generator().manual_seed(3)
+    mel_long = torch.randn(1, 80, 300, generator=g) * 2 - 4
+    for mel in (d["mel"], mel_long):
+        f0s = []
+        for dt in (torch.float32, torch.bfloat16):
+            gen = _gen(d["v2"], dt)
+            gen.inference_batch([mel], phase_vec=torch.zeros(1, 9, 1), noise=torch.zeros(1, 9, mel.shape[-1] * gen.hop))
+            prog = gen.program([mel.shape[-1]])
+            assert (dt == torch.bfloat16) == hasattr(prog, "hsplit")
+            f0s.append(prog.f0[:mel.shape[-1]].clone().cpu())
+        scale = max(1.0, f0s[0].abs().max().item())
+        print("f0 split error", (f0s[1] - f0s[0]).abs().max().item() / scale)
+        assert (f0s[1] - f0s[0]).abs().max().item() < 1e-4 * scale, (f0s[1] - f0s[0]).abs().max().item()
+    assert (f0s[1][:0].numel() == 0)
+    gen = _gen(d["v2"], torch.bfloat16)
+    gen.inference_batch([d["mel"]], phase_vec=d["phase_vec"], noise=d["noise"])
+    f0 = gen.program([T]).f0[:T].cpu()
+    assert (f0 - d["f0"][0]).abs().max().item() < 1e-4 * max(1.0, d["f0"].abs().max().item())
