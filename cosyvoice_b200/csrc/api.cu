@@ -48,6 +48,8 @@ int launch_reflect_row0(void*, int, int, int, const Layout&, cudaStream_t);
 int launch_ffn_fused(const void*, int, const void*, const float*, const void*, const float*, float*, int, void*, int,
                      const cvb200_layout&, cudaStream_t);
 int launch_split3_bf16(const float*, int, int, int, void*, int, long long, cudaStream_t);
+int launch_fade_in_out(float*, long long, int, const float*, long long, int, const double*, int, int, cudaStream_t);
+int launch_interp_linear(const float*, long long, int, float*, long long, int, int, cudaStream_t);
 int launch_anti_alias_rows(const void*, int, int, void*, int, int, const float*, const float*, const float*, int,
                            const Layout&, cudaStream_t);
 int launch_anti_alias_nct(const void*, void*, int, int, int, int, const float*, const float*, const float*, const float*,
@@ -98,6 +100,16 @@ int cvb200_ffn_fused(const void* a, int lda, const void* w1, const float* b1, co
 
 int cvb200_split3_bf16(const float* x, int ldx, int C, int cpad, void* out, int ldo, int64_t rows, void* stream) {
   return launch_split3_bf16(x, ldx, C, cpad, out, ldo, (long long)rows, ST(stream));
+}
+
+int cvb200_fade_in_out(float* x, int64_t ldx, int x_len, const float* prev, int64_t ldp, int prev_len,
+                       const double* window, int window_len, int rows, void* stream) {
+  return launch_fade_in_out(x, (long long)ldx, x_len, prev, (long long)ldp, prev_len, window, window_len, rows, ST(stream));
+}
+
+int cvb200_interp_linear(const float* x, int64_t ldx, int t_in, float* out, int64_t ldo, int t_out, int rows,
+                         void* stream) {
+  return launch_interp_linear(x, (long long)ldx, t_in, out, (long long)ldo, t_out, rows, ST(stream));
 }
 
 int cvb200_layernorm(const float* x, int ldx, void* out, int ldo, int out_dt, const float* gamma, const float* beta,

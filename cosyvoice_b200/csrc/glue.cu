@@ -247,6 +247,44 @@ __global__ void __launch_bounds__(256) split3_bf16_kernel(const float* __restric
   o[2 * cpad] = h3;
 }
 
+// ---------------------------------------------------------------------------- token2wav glue
+// Cross-fade of a streamed chunk with the tail kept from the previous one (cosyvoice/utils/common.py:149-157, called
+// from cli/model.py:150,163,174): x[r, i] = x[r, i] * w[i] + prev[r, prev_len - n + i] * w[n + i] for i < n.  The
+// reference multiplies fp32 tensors by a float64 numpy window, so the arithmetic is double and the result is rounded
+// to fp32 once; explicit _rn intrinsics keep the compiler from contracting the two products into an FMA.
+__global__ void __launch_bounds__(256) fade_in_out_kernel(float* __restrict__ x, long long ldx,
+                                                          const float* __restrict__ prev, long long ldp, int prev_len,
+                                                          const double* __restrict__ window, int n, long long total) {
+  pdl_sync();
+  const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= total) return;
+  const int i = (int)(idx % n);
+  const long long r = idx / n;
+  const double a = __dmul_rn((double)x[r * ldx + i], window[i]);
+  const double b = __dmul_rn((double)prev[r * ldp + prev_len - n + i], window[n + i]);
+  x[r * ldx + i] = __double2float_rn(__dadd_rn(a, b));
+}
+
+// F.interpolate(mel, size=t_out, mode='linear') with align_corners=False (cli/model.py:171, speed != 1.0):
+// src = (j + 0.5) * t_in / t_out - 0.5 clamped at 0, out = (1 - l) * x[i0] + l * x[min(i0 + 1, t_in - 1)], with the
+// FMA placement of ATen's CPU kernel so that the result is bit-identical to the reference's (tests/golden/token2wav.pt).
+__global__ void __launch_bounds__(256) interp_linear_kernel(const float* __restrict__ x, long long ldx, int t_in,
+                                                            float* __restrict__ out, long long ldo, int t_out,
+                                                            long long total) {
+  pdl_sync();
+  const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= total) return;
+  const int j = (int)(idx % t_out);
+  const long long r = idx / t_out;
+  const float scale = (float)t_in / (float)t_out;
+  float src = __fmaf_rn(scale, (float)j + 0.5f, -0.5f);
+  src = src < 0.f ? 0.f : src;
+  const int i0 = min((int)src, t_in - 1);
+  const int i1 = i0 + (i0 < t_in - 1 ? 1 : 0);
+  const float l1 = src - (float)i0, l0 = 1.f - l1;
+  out[r * ldo + j] = __fmaf_rn(l0, x[r * ldx + i0], __fmul_rn(l1, x[r * ldx + i1]));
+}
+
 // ---------------------------------------------------------------------------- layout transposes
 // [B, C, T] (fp32) -> time-major rows.  32x32 smem tile transpose; grid (row tiles of 32, C tiles of 32).
 __global__ void __launch_bounds__(256) nct_to_rows_kernel(const float* __restrict__ src, long long seq_stride,
@@ -358,6 +396,31 @@ int launch_split3_bf16(const float* x, int ldx, int C, int cpad, void* out, int 
   if (total <= 0) return CVB_OK;
   CVB_CUDA(launch_pdl(split3_bf16_kernel, dim3((unsigned)((total + 255) / 256)), dim3(256), 0, st, x, ldx, C, cpad,
                       reinterpret_cast<__nv_bfloat16*>(out), ldo, total));
+  CVB_LAUNCH_CHECK();
+  return CVB_OK;
+}
+
+int launch_fade_in_out(float* x, long long ldx, int x_len, const float* prev, long long ldp, int prev_len,
+                       const double* window, int window_len, int rows, cudaStream_t st) {
+  const int n = window_len / 2;
+  CVB_REQUIRE(x && prev && window && rows >= 0 && window_len >= 0, "fade_in_out: bad arguments");
+  // the reference's slice assignment raises on a shape mismatch when either side is shorter than the overlap
+  CVB_REQUIRE(x_len >= n && prev_len >= n, "fade_in_out: chunk or kept tail shorter than the overlap");
+  const long long total = (long long)rows * n;
+  if (total <= 0) return CVB_OK;
+  CVB_CUDA(launch_pdl(fade_in_out_kernel, dim3((unsigned)((total + 255) / 256)), dim3(256), 0, st, x, ldx, prev, ldp,
+                      prev_len, window, n, total));
+  CVB_LAUNCH_CHECK();
+  return CVB_OK;
+}
+
+int launch_interp_linear(const float* x, long long ldx, int t_in, float* out, long long ldo, int t_out, int rows,
+                         cudaStream_t st) {
+  CVB_REQUIRE(x && out && t_in > 0 && t_out >= 0 && rows >= 0, "interp_linear: bad arguments");
+  const long long total = (long long)rows * t_out;
+  if (total <= 0) return CVB_OK;
+  CVB_CUDA(launch_pdl(interp_linear_kernel, dim3((unsigned)((total + 255) / 256)), dim3(256), 0, st, x, ldx, t_in, out,
+                      ldo, t_out, total));
   CVB_LAUNCH_CHECK();
   return CVB_OK;
 }

@@ -277,3 +277,28 @@ def rows_to_nct(src, out, lay: SeqLayout, C_: Optional[int] = None):
     assert src.dtype == torch.float32 and out.dtype == torch.float32 and out.stride(2) == 1
     _lib.check(_lib.load().cvb200_rows_to_nct(src.data_ptr(), src.stride(0), C_ or out.shape[1], out.data_ptr(),
                                               out.stride(0), out.stride(1), C.byref(lay.c), _stream()), "rows_to_nct")
+
+
+def fade_in_out(x: torch.Tensor, prev: torch.Tensor, window: torch.Tensor) -> torch.Tensor:
+    """In place on x [..., L]: utils/common.py:149-157 with the float64 window [2n] resident on the device.
+    x and prev are contiguous with the same leading shape (mel [1,80,T] or speech [1,L])."""
+    _require_cuda(x, prev, window)
+    assert x.dtype == torch.float32 and prev.dtype == torch.float32 and window.dtype == torch.float64
+    assert x.is_contiguous() and prev.is_contiguous() and window.is_contiguous()
+    assert x.shape[:-1] == prev.shape[:-1], (x.shape, prev.shape)
+    L, Lp = x.shape[-1], prev.shape[-1]
+    rows = x.numel() // L if L else 0
+    _lib.check(_lib.load().cvb200_fade_in_out(x.data_ptr(), L, L, prev.data_ptr(), Lp, Lp, window.data_ptr(),
+                                              window.numel(), rows, _stream()), "fade_in_out")
+    return x
+
+
+def interp_linear(x: torch.Tensor, t_out: int) -> torch.Tensor:
+    """x fp32 [1, C, T] -> [1, C, t_out], F.interpolate(mode='linear', align_corners=False) (cli/model.py:171)."""
+    _require_cuda(x)
+    assert x.dtype == torch.float32 and x.dim() == 3
+    x = x.contiguous()
+    out = torch.empty(x.shape[0], x.shape[1], t_out, dtype=torch.float32, device=x.device)
+    _lib.check(_lib.load().cvb200_interp_linear(x.data_ptr(), x.shape[2], x.shape[2], out.data_ptr(), t_out, t_out,
+                                                x.shape[0] * x.shape[1], _stream()), "interp_linear")
+    return out

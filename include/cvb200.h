@@ -149,6 +149,19 @@ int cvb200_ffn_fused(const void* a, int lda, const void* w1, const float* b1, co
  * run on the bf16 tensor cores with split operands: one tap GEMM over the cross terms x_i * w_k of lowest order. */
 int cvb200_split3_bf16(const float* x, int ldx, int C, int cpad, void* out, int ldo, int64_t rows, void* stream);
 
+/* Streaming cross-fade, in place on x [rows, x_len] (row pitch ldx floats): with n = window_len / 2,
+ * x[r, i] = x[r, i] * window[i] + prev[r, prev_len - n + i] * window[n + i] for i < n, computed in double and rounded
+ * to fp32 once -- fade_in_out, cosyvoice/utils/common.py:149-157 (the reference does it on the host after two .cpu()
+ * copies; cli/model.py:150 for the mel overlap, :163/:174 and :354/:365 for the speech overlap).  window is the float64
+ * np.hamming(2 * n) table in device memory.  CVB200_ERR_INVALID when x_len or prev_len < n (the reference raises). */
+int cvb200_fade_in_out(float* x, int64_t ldx, int x_len, const float* prev, int64_t ldp, int prev_len,
+                       const double* window, int window_len, int rows, void* stream);
+
+/* Speed change on the generated mel: F.interpolate(tts_mel, size=t_out, mode='linear') of cli/model.py:171 / :362
+ * (align_corners=False) over rows = 80 mel bins; x [rows, t_in] -> out [rows, t_out]. */
+int cvb200_interp_linear(const float* x, int64_t ldx, int t_in, float* out, int64_t ldo, int t_out, int rows,
+                         void* stream);
+
 /* LayerNorm(256) over channels of each row: flow/components/transformer.py:195,231,262,300 */
 int cvb200_layernorm(const float* x, int ldx, void* out, int ldo, int out_dt, const float* gamma,
                      const float* beta, int rows, int C, float eps, void* stream);

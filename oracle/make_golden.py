@@ -159,6 +159,39 @@ def bigvgan(topology="24k100"):
     _save(f"bigvgan_{topology}.pt", dict(weights_seed=2, topology=topology, feat=feat, spk=spk, wav=wav))
 
 
+def token2wav():
+    """The REAL CosyVoiceModel / CosyVoice2Model (cli/model.py) driven over the stub flow / stub vocoder of
+    oracle/token2wav_ref.py: pins the restatement of the streaming glue (overlap fade, hift cache, speed)."""
+    R.setup()
+    from types import SimpleNamespace
+    from cosyvoice.cli.model import CosyVoiceModel, CosyVoice2Model
+    from oracle import token2wav_ref as T
+    out = {}
+    m1 = CosyVoiceModel(llm=SimpleNamespace(), flow=T.StubFlow(), hift=T.StubHift(T.SCENARIO_V1["hop"]), fp16=False,
+                        sr=T.SCENARIO_V1["sr"])
+    m1.device = torch.device("cpu")
+    outs, state = T.run_scenario_v1(m1)
+    out["v1"] = dict(outs=[o.clone() for o in outs], state={k: (v.clone() if torch.is_tensor(v) else v)
+                                                            for k, v in state.items()},
+                     flow_calls=list(m1.flow.calls))
+    m2 = CosyVoice2Model(llm=SimpleNamespace(), flow=T.StubFlow(input_frame_rate=25), hift=T.StubHift(T.SCENARIO_V2["hop"]),
+                         fp16=False)
+    m2.device = torch.device("cpu")
+    outs, state = T.run_scenario_v2(m2)
+    out["v2"] = dict(outs=[o.clone() for o in outs], state={k: v.clone() for k, v in state.items()},
+                     flow_calls=list(m2.flow.calls))
+    # the reference's fade_in_out alone, on random data (utils/common.py:149-157)
+    from cosyvoice.utils.common import fade_in_out
+    g = _gen(900)
+    a, b = torch.randn(1, 80, 50, generator=g), torch.randn(1, 80, 34, generator=g)
+    w = np.hamming(2 * 34)
+    out["fade"] = dict(a=a, b=b, n=34, out=fade_in_out(a, b, w))
+    x = torch.randn(1, 80, 37, generator=g)
+    out["interp"] = dict(x=x, sizes=[28, 37, 46, 111],
+                         outs=[torch.nn.functional.interpolate(x, size=n, mode="linear") for n in (28, 37, 46, 111)])
+    _save("token2wav.pt", out)
+
+
 if __name__ == "__main__":
     import warnings
     warnings.filterwarnings("ignore")
@@ -171,3 +204,4 @@ if __name__ == "__main__":
     hift(True)
     act1d()
     bigvgan("24k100")
+    token2wav()

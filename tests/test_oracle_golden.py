@@ -85,3 +85,31 @@ def test_bigvgan_trunk_matches_reference(golden_dir):
     sd = init_weights.bigvgan_sd(d["topology"], seed=d["weights_seed"])
     wav = bigvgan_ref.trunk_forward(sd, d["feat"], d["spk"], d["topology"])
     _close(wav, d["wav"], atol=1e-4)
+
+
+# ---- streaming glue: oracle/token2wav_ref.py against the real CosyVoiceModel / CosyVoice2Model ----
+def test_fade_in_out_and_interp_match_reference(golden_dir):
+    import numpy as np
+    from oracle import token2wav_ref as T
+    d = _load(golden_dir, "token2wav.pt")
+    f = d["fade"]
+    assert torch.equal(T.fade_in_out_ref(f["a"], f["b"], np.hamming(2 * f["n"])), f["out"])      # bit-exact
+    for n, ref in zip(d["interp"]["sizes"], d["interp"]["outs"]):
+        assert torch.equal(T.interp_linear_ref(d["interp"]["x"], n), ref)
+
+
+@pytest.mark.parametrize("ver", ["v1", "v2"])
+def test_token2wav_oracle_matches_reference_session(golden_dir, ver):
+    from oracle import token2wav_ref as T
+    d = _load(golden_dir, "token2wav.pt")[ver]
+    if ver == "v1":
+        m = T.Token2WavRef(T.StubFlow(), T.StubHift(T.SCENARIO_V1["hop"]), sr=T.SCENARIO_V1["sr"])
+        outs, state = T.run_scenario_v1(m)
+    else:
+        m = T.Token2Wav2Ref(T.StubFlow(input_frame_rate=25), T.StubHift(T.SCENARIO_V2["hop"]))
+        outs, state = T.run_scenario_v2(m)
+    assert [tuple(c) for c in m.flow.calls] == [tuple(c) for c in d["flow_calls"]]
+    for i, (o, ref) in enumerate(zip(outs, d["outs"])):
+        assert torch.equal(o, ref), f"chunk {i}"                    # fades are double -> fp32, stubs dyadic: bit-exact
+    for k, v in d["state"].items():
+        assert torch.equal(state[k], v) if torch.is_tensor(v) else tuple(state[k]) == tuple(v), k
