@@ -18,6 +18,11 @@ try:
 except Exception:
     pass
 filt = kaiser_sinc_filter12(dev)
+REF = None
+if "--ref" in sys.argv:       # the reference's own fwd_cuda built for sm_100a (oracle/build_ref.py): the kernel to beat
+    from oracle import build_ref
+    REF = build_ref.load()
+    assert REF is not None, "oracle/_ref not built"
 
 
 def timed(fn, reps=5):
@@ -62,4 +67,10 @@ for dt in (torch.float32, torch.bfloat16):
         gb = 2 * x.numel() * x.element_size() / 1e9
         print(json.dumps({"kernel": "anti_alias_act_nct", "shape": [B, c, T], "dtype": str(dt)[6:], "ms": round(ms, 4),
                           "algorithmic_GBps": round(gb / ms * 1e3, 1), "frac": round(gb / ms * 1e3 / PEAK, 3)}))
+        if REF is not None:
+            f3 = filt.reshape(1, 1, -1)
+            ms_r = timed(lambda: REF.forward(x, f3, f3, al, be))
+            print(json.dumps({"kernel": "reference fwd_cuda (sm_100a build, --use_fast_math)", "shape": [B, c, T],
+                              "dtype": str(dt)[6:], "ms": round(ms_r, 4), "algorithmic_GBps": round(gb / ms_r * 1e3, 1),
+                              "frac": round(gb / ms_r * 1e3 / PEAK, 3), "speedup_ours": round(ms_r / ms, 2)}))
         del x, y
