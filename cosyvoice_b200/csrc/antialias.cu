@@ -41,6 +41,20 @@ __device__ __forceinline__ float2 ffma2(float2 a, float2 b, float2 c) { return _
 __device__ __forceinline__ float2 fmul2(float2 a, float2 b) { return __fmul2_rn(a, b); }
 #endif
 
+// sin for the fp32-output kernels: two-term Cody-Waite reduction to [-pi, pi] and the SFU on the remainder.  Absolute
+// error <= 2^-21.4 at any magnitude the activations reach (plain __sinf loses accuracy with |x|; libm sinf costs ~4x
+// the instructions, which made the fp32 kernels compute-bound at half the bf16 rate).  -DAA_LIBM_SIN restores sinf.
+__device__ __forceinline__ float sin_reduced(float t) {
+#ifdef AA_LIBM_SIN
+  return sinf(t);
+#else
+  const float k = rintf(t * 0.15915494309189535f);
+  float r = fmaf(k, -6.2831854820251465f, t);
+  r = fmaf(k, 1.7484555e-7f, r);
+  return __sinf(r);
+#endif
+}
+
 template <bool FAST>
 __device__ __forceinline__ float2 snake_beta2(float2 up, float2 ea, float2 ib) {
   // z = up + sin^2(up e^alpha) ib
@@ -50,8 +64,8 @@ __device__ __forceinline__ float2 snake_beta2(float2 up, float2 ea, float2 ib) {
     s.x = __sinf(t.x);
     s.y = __sinf(t.y);
   } else {
-    s.x = sinf(t.x);
-    s.y = sinf(t.y);
+    s.x = sin_reduced(t.x);
+    s.y = sin_reduced(t.y);
   }
   return ffma2(fmul2(s, ib), s, up);
 }

@@ -299,6 +299,30 @@ def test_anti_alias_activation_nct_matches_reference_golden(golden_dir, dtype):
     assert e.shape == (1, 4, 0)
 
 
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("T", [4096, 4097, 8191, 12289, 5])
+def test_anti_alias_nct_vector_staging_any_alignment(dtype, T):
+    """The [B,C,T] kernel stages with 16-byte accesses aligned to the global address: odd T (rows start at odd element
+    offsets), chunk boundaries at 4096 and a base pointer that is itself only element-aligned."""
+    from oracle import bigvgan_ref
+    g = torch.Generator().manual_seed(T)
+    B, Cc = 2, 3
+    x = (torch.randn(B, Cc, T, generator=g) * 2).to(dtype)
+    al, be = torch.randn(Cc, generator=g) * 0.3, torch.randn(Cc, generator=g) * 0.3
+    filt = bigvgan_ref.kaiser_sinc_filter()
+    want = bigvgan_ref.anti_alias_act(x.double(), al.double(), be.double(), filt.double())
+    tol = 2e-5 if dtype == torch.float32 else want.abs().max().item() * 2.0 ** -8 * 1.05 + 1e-6
+    for shift in (0, 1, 3):
+        flat = torch.zeros(B * Cc * T + shift + 16, dtype=dtype, device=DEV)
+        xv = flat[shift:shift + B * Cc * T].view(B, Cc, T)
+        xv.copy_(x.to(DEV))
+        assert xv.is_contiguous() and xv.data_ptr() == flat.data_ptr() + shift * flat.element_size()
+        y = ops.anti_alias_act_nct(xv, filt.to(DEV), filt.to(DEV), al.to(DEV), be.to(DEV))
+        _sync()
+        assert (y.double().cpu() - want).abs().max().item() <= tol, (shift, T)
+        assert flat[shift + B * Cc * T:].abs().max().item() == 0 and (shift == 0 or flat[:shift].abs().max().item() == 0)
+
+
 def test_anti_alias_activation_rows_varlen():
     from oracle import bigvgan_ref
     g = torch.Generator().manual_seed(10)
