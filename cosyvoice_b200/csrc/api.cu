@@ -50,6 +50,7 @@ int launch_ffn_fused(const void*, int, const void*, const float*, const void*, c
 int launch_split3_bf16(const float*, int, int, int, void*, int, long long, cudaStream_t);
 int launch_fade_in_out(float*, long long, int, const float*, long long, int, const double*, int, int, cudaStream_t);
 int launch_interp_linear(const float*, long long, int, float*, long long, int, int, cudaStream_t);
+int launch_pcm16(const float*, short*, float, long long, cudaStream_t);
 int launch_anti_alias_rows(const void*, int, int, void*, int, int, const float*, const float*, const float*, int,
                            const Layout&, cudaStream_t);
 int launch_anti_alias_nct(const void*, void*, int, int, int, int, const float*, const float*, const float*, const float*,
@@ -110,6 +111,10 @@ int cvb200_fade_in_out(float* x, int64_t ldx, int x_len, const float* prev, int6
 int cvb200_interp_linear(const float* x, int64_t ldx, int t_in, float* out, int64_t ldo, int t_out, int rows,
                          void* stream) {
   return launch_interp_linear(x, (long long)ldx, t_in, out, (long long)ldo, t_out, rows, ST(stream));
+}
+
+int cvb200_pcm16(const float* wav, int16_t* out, float scale, int64_t n, void* stream) {
+  return launch_pcm16(wav, reinterpret_cast<short*>(out), scale, (long long)n, ST(stream));
 }
 
 int cvb200_layernorm(const float* x, int ldx, void* out, int ldo, int out_dt, const float* gamma, const float* beta,

@@ -285,6 +285,17 @@ __global__ void __launch_bounds__(256) interp_linear_kernel(const float* __restr
   out[r * ldo + j] = __fmaf_rn(l0, x[r * ldx + i0], __fmul_rn(l1, x[r * ldx + i1]));
 }
 
+// int16 PCM packing of a finished waveform (BigVGAN/utils.py:97-101 save_audio: audio * MAX_WAV_VALUE, .astype("int16")):
+// truncation toward zero like the numpy cast; values outside int16 saturate (the numpy cast is undefined there).
+__global__ void __launch_bounds__(256) pcm16_kernel(const float* __restrict__ wav, short* __restrict__ out, float scale,
+                                                    long long n) {
+  pdl_sync();
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const float v = fminf(fmaxf(__fmul_rn(wav[i], scale), -32768.f), 32767.f);
+  out[i] = (short)__float2int_rz(v);
+}
+
 // ---------------------------------------------------------------------------- layout transposes
 // [B, C, T] (fp32) -> time-major rows.  32x32 smem tile transpose; grid (row tiles of 32, C tiles of 32).
 __global__ void __launch_bounds__(256) nct_to_rows_kernel(const float* __restrict__ src, long long seq_stride,
@@ -421,6 +432,14 @@ int launch_interp_linear(const float* x, long long ldx, int t_in, float* out, lo
   if (total <= 0) return CVB_OK;
   CVB_CUDA(launch_pdl(interp_linear_kernel, dim3((unsigned)((total + 255) / 256)), dim3(256), 0, st, x, ldx, t_in, out,
                       ldo, t_out, total));
+  CVB_LAUNCH_CHECK();
+  return CVB_OK;
+}
+
+int launch_pcm16(const float* wav, short* out, float scale, long long n, cudaStream_t st) {
+  if (n == 0) return CVB_OK;
+  CVB_REQUIRE(wav && out && n > 0, "pcm16: bad arguments");
+  CVB_CUDA(launch_pdl(pcm16_kernel, dim3((unsigned)((n + 255) / 256)), dim3(256), 0, st, wav, out, scale, n));
   CVB_LAUNCH_CHECK();
   return CVB_OK;
 }

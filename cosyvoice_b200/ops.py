@@ -302,3 +302,13 @@ def interp_linear(x: torch.Tensor, t_out: int) -> torch.Tensor:
     _lib.check(_lib.load().cvb200_interp_linear(x.data_ptr(), x.shape[2], x.shape[2], out.data_ptr(), t_out, t_out,
                                                 x.shape[0] * x.shape[1], _stream()), "interp_linear")
     return out
+
+
+def pcm16(wav: torch.Tensor, scale: float = 32768.0) -> torch.Tensor:
+    """fp32 waveform -> int16 PCM on the device (BigVGAN/utils.py:97-101 save_audio's packing)."""
+    _require_cuda(wav)
+    assert wav.dtype == torch.float32
+    wav = wav.contiguous()
+    out = torch.empty(wav.shape, dtype=torch.int16, device=wav.device)
+    _lib.check(_lib.load().cvb200_pcm16(wav.data_ptr(), out.data_ptr(), scale, wav.numel(), _stream()), "pcm16")
+    return out

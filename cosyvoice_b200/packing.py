@@ -24,11 +24,15 @@ Atom = Tuple[int, int, torch.Tensor]      # (row_off, col_off, w_tap [N, c_in])
 
 
 def fold_weight_norm(sd: Dict[str, torch.Tensor], prefix: str) -> torch.Tensor:
-    """Old-style torch.nn.utils.weight_norm(dim=0) pair -> plain weight
+    """torch.nn.utils.weight_norm(dim=0) pair (old `weight_g/weight_v` or parametrized `original0/original1` keys, as
+    the released hift.pt files carry) -> plain weight
     (cosyvoice/hifigan/generator.py:25-26; the reference's own remove_weight_norm is broken, :327)."""
     if prefix + "weight" in sd:
         return sd[prefix + "weight"]
-    v, g = sd[prefix + "weight_v"], sd[prefix + "weight_g"]
+    if prefix + "parametrizations.weight.original1" in sd:      # torch.nn.utils.parametrizations.weight_norm checkpoints
+        v, g = sd[prefix + "parametrizations.weight.original1"], sd[prefix + "parametrizations.weight.original0"]
+    else:
+        v, g = sd[prefix + "weight_v"], sd[prefix + "weight_g"]
     n = v.reshape(v.shape[0], -1).norm(dim=1).reshape(-1, *([1] * (v.dim() - 1)))
     return v * (g / n)
 

@@ -162,6 +162,10 @@ int cvb200_fade_in_out(float* x, int64_t ldx, int x_len, const float* prev, int6
 int cvb200_interp_linear(const float* x, int64_t ldx, int t_in, float* out, int64_t ldo, int t_out, int rows,
                          void* stream);
 
+/* int16 PCM wire format of a finished waveform: out[i] = (int16) trunc(wav[i] * scale), saturated to [-32768, 32767].
+ * save_audio, cosyvoice/BigVGAN/utils.py:97-101 (scale = MAX_WAV_VALUE = 32768, numpy .astype("int16")). */
+int cvb200_pcm16(const float* wav, int16_t* out, float scale, int64_t n, void* stream);
+
 /* LayerNorm(256) over channels of each row: flow/components/transformer.py:195,231,262,300 */
 int cvb200_layernorm(const float* x, int ldx, void* out, int ldo, int out_dt, const float* gamma,
                      const float* beta, int rows, int C, float eps, void* stream);
