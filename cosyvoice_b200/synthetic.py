@@ -233,3 +233,77 @@ def flow_inputs(n_utt: int, gen_frames, prompt_frames: int = 281, first_index: i
         conds.append(c)
         zs.append(torch.randn(1, 80, T, generator=_g(4321 + first_index + i)))
     return mus, spks, conds, zs
+
+
+# ----------------------------------------------------------------------------- flow front-end
+def flow_frontend_sd(v2: bool, seed: int = 2) -> SD:
+    """Everything of MaskedDiffWithXvec / CausalMaskedDiffWithXvec except `decoder.*`: input_embedding,
+    spk_embed_affine_layer, encoder (ConformerEncoder | UpsampleConformerEncoder, d 512, 8 heads, FFN 2048, 6 (+4) blocks,
+    rel-pos attention), encoder_proj and, v1 only, the InterpolateRegulator (flow/flow.py:25-62,163-203 with the yaml
+    numbers of examples/tts_vc/cosyvoice{,2}/conf/cosyvoice.yaml)."""
+    g = _g(seed)
+    sd: SD = {}
+    D, H, FF, V, SPK = 512, 8, 2048, (6561 if v2 else 4096), (192 if v2 else 512)
+    sd["input_embedding.weight"] = torch.randn(V, D, generator=g)
+    sd["spk_embed_affine_layer.weight"] = _uniform_default(g, (80, SPK), SPK)
+    sd["spk_embed_affine_layer.bias"] = _bias(g, 80)
+
+    def lin(p, n, k, bias=True):
+        sd[p + "weight"] = _uniform_default(g, (n, k), k)
+        if bias:
+            sd[p + "bias"] = _bias(g, n)
+
+    def embed(p):
+        lin(p + "out.0.", D, D)
+        _affine(g, sd, p + "out.1.weight", p + "out.1.bias", D)
+
+    def layer(p):
+        for n in ("q", "k", "v", "out"):
+            lin(p + f"self_attn.linear_{n}.", D, D)
+        lin(p + "self_attn.linear_pos.", D, D, bias=False)
+        b = math.sqrt(6.0 / (H + D // H))          # xavier_uniform on [H, D/H] (transformer/attention.py:219-220)
+        sd[p + "self_attn.pos_bias_u"] = (torch.rand(H, D // H, generator=g) * 2 - 1) * b
+        sd[p + "self_attn.pos_bias_v"] = (torch.rand(H, D // H, generator=g) * 2 - 1) * b
+        lin(p + "feed_forward.w_1.", FF, D)
+        lin(p + "feed_forward.w_2.", D, FF)
+        _affine(g, sd, p + "norm_ff.weight", p + "norm_ff.bias", D)
+        _affine(g, sd, p + "norm_mha.weight", p + "norm_mha.bias", D)
+
+    embed("encoder.embed.")
+    if v2:
+        sd["encoder.pre_lookahead_layer.conv1.weight"] = _uniform_default(g, (D, D, 4), D * 4)
+        sd["encoder.pre_lookahead_layer.conv1.bias"] = _bias(g, D)
+        sd["encoder.pre_lookahead_layer.conv2.weight"] = _uniform_default(g, (D, D, 3), D * 3)
+        sd["encoder.pre_lookahead_layer.conv2.bias"] = _bias(g, D)
+    for i in range(6):
+        layer(f"encoder.encoders.{i}.")
+    if v2:
+        sd["encoder.up_layer.conv.weight"] = _uniform_default(g, (D, D, 5), D * 5)
+        sd["encoder.up_layer.conv.bias"] = _bias(g, D)
+        embed("encoder.up_embed.")
+        for i in range(4):
+            layer(f"encoder.up_encoders.{i}.")
+    _affine(g, sd, "encoder.after_norm.weight", "encoder.after_norm.bias", D)
+    lin("encoder_proj.", 80, D)
+    if not v2:
+        for i in range(4):
+            sd[f"length_regulator.model.{3 * i}.weight"] = _uniform_default(g, (80, 80, 3), 240)
+            sd[f"length_regulator.model.{3 * i}.bias"] = _bias(g, 80)
+            _affine(g, sd, f"length_regulator.model.{3 * i + 1}.weight", f"length_regulator.model.{3 * i + 1}.bias", 80)
+        sd["length_regulator.model.12.weight"] = _uniform_default(g, (80, 80, 1), 80)
+        sd["length_regulator.model.12.bias"] = _bias(g, 80)
+    return sd
+
+
+def frontend_inputs(v2: bool, n_tokens: int, n_prompt_tokens: int, seed: int):
+    """token / prompt_token int32 [1, n], prompt_feat [1, T_p, 80] time-major log-mel-like, embedding [1, spk].
+    T_p = the reference's own prompt ratio: v1 3.75 frames per token at 22.05 kHz/256 -> int(n / 25 * 22050 / 256);
+    v2 2 frames per token."""
+    g = _g(seed)
+    V, SPK = (6561, 192) if v2 else (4096, 512)
+    token = torch.randint(0, V, (1, n_tokens), generator=g, dtype=torch.int32)
+    prompt_token = torch.randint(0, V, (1, n_prompt_tokens), generator=g, dtype=torch.int32)
+    t_p = 2 * n_prompt_tokens if v2 else int(n_prompt_tokens / 25 * 22050 / 256)
+    prompt_feat = torch.randn(1, t_p, 80, generator=g) * 2 - 4
+    embedding = torch.randn(1, SPK, generator=g)
+    return token, prompt_token, prompt_feat, embedding

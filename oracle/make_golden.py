@@ -192,6 +192,62 @@ def token2wav():
     _save("token2wav.pt", out)
 
 
+class _CaptureDecoder(torch.nn.Module):
+    """Stands in for flow.decoder: records what flow.inference hands to the CFM (flow/flow.py:150-158)."""
+
+    def forward(self, mu, mask, spks, cond, n_timesteps, prompt_len=0, flow_cache=None):
+        self.seen = dict(mu=mu.clone(), mask=mask.clone(), spks=spks.clone(), cond=cond.clone(), prompt_len=prompt_len)
+        return torch.zeros_like(mu), flow_cache
+
+
+def frontend(v2: bool):
+    """flow.inference of the REAL MaskedDiffWithXvec / CausalMaskedDiffWithXvec: (a) with the decoder replaced by a
+    recorder -> the front-end's outputs (mu, spks, cond); (b) with the real CFM + estimator -> the mel."""
+    est = R.build_estimator(v2).eval()
+    est.load_state_dict(W.flow_estimator_sd(v2, seed=0), strict=True)
+    m = R.build_flow(v2, est).eval()
+    res = m.load_state_dict(W.flow_frontend_sd(v2, seed=2), strict=False)
+    assert not res.unexpected_keys and all(k.startswith("decoder.") for k in res.missing_keys), res
+    real_decoder = m.decoder
+    cases = []
+    if v2:
+        specs = [dict(n=23, n_prompt=9, chunk=0, trim=True), dict(n=23, n_prompt=9, chunk=5, trim=False),
+                 dict(n=31, n_prompt=0, chunk=0, trim=False)]
+    else:
+        specs = [dict(n=50, n_prompt=12), dict(n=30, n_prompt=0), dict(n=41, n_prompt=7)]
+    for ci, sp in enumerate(specs):
+        token, prompt_token, prompt_feat, embedding = W.frontend_inputs(v2, sp["n"], sp["n_prompt"], seed=500 + 10 * v2 + ci)
+        if v2 and sp["trim"]:       # odd prompt length -> the trim branch of flow.py:279-283
+            g = _gen(77)
+            prompt_feat = torch.cat([prompt_feat, torch.randn(1, 1, 80, generator=g)], dim=1)
+        d = dict(sp, token=token, prompt_token=prompt_token, prompt_feat=prompt_feat, embedding=embedding)
+
+        def call():
+            kw = dict(token=token.clone(), token_len=torch.tensor([token.shape[1]], dtype=torch.int32),
+                      prompt_token=prompt_token.clone(),
+                      prompt_token_len=torch.tensor([prompt_token.shape[1]], dtype=torch.int32),
+                      prompt_feat=prompt_feat.clone(),
+                      prompt_feat_len=torch.tensor([prompt_feat.shape[1]], dtype=torch.int32), embedding=embedding.clone())
+            if v2:
+                m.encoder.static_chunk_size = sp["chunk"]
+                return m.inference(**kw, n_timesteps=10)
+            return m.inference(**kw, flow_cache=torch.zeros(1, 80, 0, 2), sample_rate=22050, n_timesteps=10)
+        with torch.no_grad():
+            m.decoder = _CaptureDecoder()
+            call()
+            seen = m.decoder.seen
+            m.decoder = real_decoder
+            torch.manual_seed(4400 + ci)
+            mel, cache = call()
+        T = seen["mu"].shape[2]
+        torch.manual_seed(4400 + ci)
+        z = real_decoder.rand_noise[:, :, :T].clone() if v2 else torch.randn(1, 80, T)
+        d.update(mu=seen["mu"], spks=seen["spks"], cond=seen["cond"], prompt_len=seen["prompt_len"], z=z, mel=mel,
+                 flow_cache=cache)
+        cases.append(d)
+    _save(f"frontend_{'v2' if v2 else 'v1'}.pt", dict(weights_seed=2, estimator_seed=0, v2=v2, cases=cases))
+
+
 if __name__ == "__main__":
     import warnings
     warnings.filterwarnings("ignore")
@@ -205,3 +261,5 @@ if __name__ == "__main__":
     act1d()
     bigvgan("24k100")
     token2wav()
+    frontend(False)
+    frontend(True)

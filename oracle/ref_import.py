@@ -88,3 +88,25 @@ def build_bigvgan(topology: str = "24k100"):
                        upsample_kernel_sizes=[16, 11, 7, 2], upsample_initial_channel=1536,
                        speaker_embedding_dim=512)
     raise ValueError(topology)
+
+
+def build_flow(v2: bool, estimator=None):
+    """MaskedDiffWithXvec (v1) / CausalMaskedDiffWithXvec (v2) with the yaml numbers
+    (examples/tts_vc/cosyvoice/conf/cosyvoice.yaml:65-112, cosyvoice2/conf/cosyvoice.yaml:31-80)."""
+    setup()
+    from cosyvoice.flow.flow import MaskedDiffWithXvec, CausalMaskedDiffWithXvec
+    from cosyvoice.flow.length_regulator import InterpolateRegulator
+    from cosyvoice.transformer.encoder import ConformerEncoder
+    from cosyvoice.transformer.upsample_encoder import UpsampleConformerEncoder
+    enc_kw = dict(output_size=512, attention_heads=8, linear_units=2048, num_blocks=6, dropout_rate=0.1,
+                  positional_dropout_rate=0.1, attention_dropout_rate=0.1, normalize_before=True, input_layer="linear",
+                  pos_enc_layer_type="rel_pos_espnet", selfattention_layer_type="rel_selfattn", input_size=512,
+                  use_cnn_module=False, macaron_style=False)
+    dec = build_cfm(v2, estimator)
+    if v2:
+        return CausalMaskedDiffWithXvec(input_size=512, output_size=80, spk_embed_dim=192, output_type="mel", vocab_size=6561,
+                                        input_frame_rate=25, only_mask_loss=True, token_mel_ratio=2, pre_lookahead_len=3,
+                                        encoder=UpsampleConformerEncoder(**enc_kw), decoder=dec)
+    return MaskedDiffWithXvec(input_size=512, output_size=80, spk_embed_dim=512, output_type="mel", vocab_size=4096,
+                              input_frame_rate=25, only_mask_loss=True, encoder=ConformerEncoder(**enc_kw),
+                              length_regulator=InterpolateRegulator(channels=80, sampling_ratios=[1, 1, 1, 1]), decoder=dec)

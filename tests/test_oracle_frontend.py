@@ -1,0 +1,71 @@
+"""Pins oracle/encoder_ref.py (flow front-end: token embedding, rel-pos Conformer encoders, length regulator, speaker
+projection) to tests/golden/frontend_v{1,2}.pt, which oracle/make_golden.py recorded from the REAL
+MaskedDiffWithXvec / CausalMaskedDiffWithXvec `inference` (flow/flow.py:108-160, 258-319).  CPU only."""
+import os
+
+import pytest
+import torch
+
+from oracle import encoder_ref as E
+from oracle import flow_ref, init_weights
+
+
+def _load(golden_dir, name):
+    return torch.load(os.path.join(golden_dir, name), weights_only=True)
+
+
+def _frontend(sd, c, v2):
+    if v2:
+        return E.frontend_v2(sd, c["token"], c["prompt_token"], c["prompt_feat"], c["embedding"], static_chunk_size=c["chunk"])
+    return E.frontend_v1(sd, c["token"], c["prompt_token"], c["prompt_feat"], c["embedding"])
+
+
+@pytest.mark.parametrize("ver", ["v1", "v2"])
+def test_frontend_matches_reference(golden_dir, ver):
+    d = _load(golden_dir, f"frontend_{ver}.pt")
+    sd = init_weights.flow_frontend_sd(d["v2"], seed=d["weights_seed"])
+    for i, c in enumerate(d["cases"]):
+        mu, spks, cond, l1, l2 = _frontend(sd, c, d["v2"])
+        assert mu.shape == c["mu"].shape and l1 + l2 == c["mu"].shape[2], i
+        assert l1 == c["prompt_len"] or d["v2"]
+        assert torch.equal(cond, c["cond"]), i
+        assert (spks - c["spks"]).abs().max() < 1e-6, i
+        err = (mu - c["mu"]).abs().max().item()
+        assert err < 2e-4, (i, err)          # fp32 re-association only (explicit gather vs rel_shift, F.linear order)
+
+
+@pytest.mark.parametrize("ver", ["v1", "v2"])
+def test_frontend_plus_cfm_matches_reference_inference(golden_dir, ver):
+    """The whole boundary call: front-end oracle -> CFM oracle == the reference's flow.inference output."""
+    d = _load(golden_dir, f"frontend_{ver}.pt")
+    v2 = d["v2"]
+    fsd = init_weights.flow_frontend_sd(v2, seed=d["weights_seed"])
+    esd = init_weights.flow_estimator_sd(v2, seed=d["estimator_seed"])
+    c = d["cases"][0]
+    mu, spks, cond, l1, l2 = _frontend(fsd, c, v2)
+    T = l1 + l2
+    mel = flow_ref.solve_euler(esd, c["z"], flow_ref.cosine_t_span(10), mu, torch.ones(1, 1, T), spks, cond, causal=v2)
+    assert mel[:, :, l1:].shape == c["mel"].shape
+    err = (mel[:, :, l1:] - c["mel"]).abs().max().item()
+    assert err < 1e-3, err
+
+
+def test_chunk_mask_is_the_references_subsequent_chunk_mask():
+    # utils/mask.py:116-124 written as the loop the reference uses
+    for T, c in ((7, 3), (10, 5), (5, 8)):
+        ref = torch.zeros(T, T, dtype=torch.bool)
+        for i in range(T):
+            ref[i, 0:min((i // c + 1) * c, T)] = True
+        assert torch.equal(E.chunk_mask(T, c), ref)
+    assert E.chunk_mask(9, 0) is None
+
+
+def test_regulator_segments_cover_the_output_once():
+    for n1, n2 in ((12, 50), (0, 30), (7, 41), (75, 250)):
+        l1, l2 = int(n1 / 25 * 22050 / 256), int(n2 / 25 * 22050 / 256)
+        segs = E.regulator_segments(n1, n2, l1, l2)
+        pos, src = 0, 0
+        for (s, n, ds, dn) in segs:
+            assert ds == pos and s == src
+            pos, src = pos + dn, src + n
+        assert pos == l1 + l2 and src == n1 + n2
