@@ -77,6 +77,12 @@ SIGNATURES = {
     "cvb200_anti_alias_act_rows": [_P, _I, _I, _P, _I, _I, _P, _P, _P, _I, _LAY, _P],
     "cvb200_nct_to_rows": [_P, _L, _L, _I, _P, _I, _I, _LAY, _P],
     "cvb200_rows_to_nct": [_P, _I, _I, _P, _L, _L, _LAY, _P],
+    "cvb200_embed_tokens": [_P, _I, _P, _I, _I, _P, _I, _I, _LAY, _P],
+    "cvb200_layernorm_seq": [_P, _I, _P, _I, _I, _P, _P, _LAY, _I, _F, _P],
+    "cvb200_relpos_attention": [_P, _I, _P, _I, _I, _I, _P, _P, _P, _I, _I, _LAY, _I, _F, _I, _P],
+    "cvb200_groupnorm1_mish": [_P, _I, _P, _I, _I, _P, _P, _I, _LAY, _F, _P],
+    "cvb200_interp_rows": [_P, _I, _LAY, _P, _I, _I, _LAY, _P, _I, _P],
+    "cvb200_l2_normalize": [_P, _P, _I, _I, _P],
 }
 _SPECIAL = {
     "cvb200_last_error": ([], C.c_char_p),

@@ -56,6 +56,14 @@ int launch_anti_alias_rows(const void*, int, int, void*, int, int, const float*,
 int launch_anti_alias_nct(const void*, void*, int, int, int, int, const float*, const float*, const float*, const float*,
                           cudaStream_t);
 
+int launch_embed_tokens(const int*, int, const float*, int, int, void*, int, int, const Layout&, cudaStream_t);
+int launch_layernorm_seq(const float*, int, void*, int, int, const float*, const float*, const Layout&, int, float, cudaStream_t);
+int launch_relpos_attention(const float*, int, const float*, int, int, int, const float*, const float*, void*, int, int,
+                            const Layout&, int, float, int, cudaStream_t);
+int launch_groupnorm1_mish(const float*, int, void*, int, int, const float*, const float*, int, const Layout&, float, cudaStream_t);
+int launch_interp_rows(const float*, int, const Layout&, void*, int, int, const Layout&, const int*, int, cudaStream_t);
+int launch_l2_normalize(const float*, float*, int, int, cudaStream_t);
+
 }  // namespace cvb
 
 using namespace cvb;
@@ -232,6 +240,43 @@ int cvb200_rows_to_nct(const float* src, int lds, int C, float* out, int64_t seq
                        const cvb200_layout* lay, void* stream) {
   NEED(src, "src"); NEED(out, "out"); NEED(lay, "layout");
   return launch_rows_to_nct(src, lds, C, out, (long long)seq_stride, (long long)c_stride, *lay, ST(stream));
+}
+
+int cvb200_embed_tokens(const int32_t* tokens, int tok_ld, const float* table, int vocab, int C, void* out, int ldo, int out_dt,
+                        const cvb200_layout* lay, void* stream) {
+  NEED(tokens, "tokens"); NEED(table, "table"); NEED(out, "out"); NEED(lay, "layout");
+  return launch_embed_tokens(tokens, tok_ld, table, vocab, C, out, ldo, out_dt, *lay, ST(stream));
+}
+
+int cvb200_layernorm_seq(const float* x, int ldx, void* out, int ldo, int out_dt, const float* gamma, const float* beta,
+                         const cvb200_layout* lay, int C, float eps, void* stream) {
+  NEED(x, "x"); NEED(out, "out"); NEED(gamma, "gamma"); NEED(beta, "beta"); NEED(lay, "layout");
+  return launch_layernorm_seq(x, ldx, out, ldo, out_dt, gamma, beta, *lay, C, eps, ST(stream));
+}
+
+int cvb200_relpos_attention(const float* qkv, int ld, const float* pos, int ldp, int center, int n_rel, const float* bias_u,
+                            const float* bias_v, void* out, int ldo, int out_dt, const cvb200_layout* lay, int heads,
+                            float scale, int chunk, void* stream) {
+  NEED(qkv, "qkv"); NEED(pos, "pos"); NEED(bias_u, "pos_bias_u"); NEED(bias_v, "pos_bias_v"); NEED(out, "out"); NEED(lay, "layout");
+  return launch_relpos_attention(qkv, ld, pos, ldp, center, n_rel, bias_u, bias_v, out, ldo, out_dt, *lay, heads, scale, chunk,
+                                 ST(stream));
+}
+
+int cvb200_groupnorm1_mish(const float* h, int ldh, void* out, int ldo, int out_dt, const float* gamma, const float* beta,
+                           int C, const cvb200_layout* lay, float eps, void* stream) {
+  NEED(h, "h"); NEED(out, "out"); NEED(gamma, "gamma"); NEED(beta, "beta"); NEED(lay, "layout");
+  return launch_groupnorm1_mish(h, ldh, out, ldo, out_dt, gamma, beta, C, *lay, eps, ST(stream));
+}
+
+int cvb200_interp_rows(const float* x, int ldx, const cvb200_layout* src_lay, void* out, int ldo, int out_dt,
+                       const cvb200_layout* dst_lay, const int32_t* segs, int C, void* stream) {
+  NEED(x, "x"); NEED(out, "out"); NEED(src_lay, "src layout"); NEED(dst_lay, "dst layout"); NEED(segs, "segs");
+  return launch_interp_rows(x, ldx, *src_lay, out, ldo, out_dt, *dst_lay, segs, C, ST(stream));
+}
+
+int cvb200_l2_normalize(const float* x, float* out, int S, int K, void* stream) {
+  NEED(x, "x"); NEED(out, "out");
+  return launch_l2_normalize(x, out, S, K, ST(stream));
 }
 
 }  // extern "C"

@@ -312,3 +312,72 @@ def pcm16(wav: torch.Tensor, scale: float = 32768.0) -> torch.Tensor:
     out = torch.empty(wav.shape, dtype=torch.int16, device=wav.device)
     _lib.check(_lib.load().cvb200_pcm16(wav.data_ptr(), out.data_ptr(), scale, wav.numel(), _stream()), "pcm16")
     return out
+
+
+# ---- flow front-end (csrc/encoder.cu) -------------------------------------------------------------------------------
+def embed_tokens_op(tokens: torch.Tensor, table: torch.Tensor, out: torch.Tensor, lay: SeqLayout) -> Op:
+    """tokens int32 [n_seq, tok_ld]; table fp32 [V, C]; out rows [rows, >=C] (flow/flow.py:131-135)."""
+    _require_cuda(tokens, table, out)
+    assert tokens.dtype == torch.int32 and tokens.dim() == 2 and tokens.stride(1) == 1 and table.dtype == torch.float32
+    assert table.is_contiguous() and tokens.shape[0] == lay.n_seq
+    lib = _lib.load()
+    layc = lay.c
+    args = (tokens.data_ptr(), tokens.stride(0), table.data_ptr(), table.shape[0], table.shape[1], out.data_ptr(),
+            out.stride(0), dt_of(out), C.byref(layc))
+    keep = (tokens, table, out, lay, layc)
+    return lambda _k=keep: _lib.check(lib.cvb200_embed_tokens(*args, _stream()), "embed_tokens")
+
+
+def layernorm_seq_op(x, out, gamma, beta, lay: SeqLayout, eps: float) -> Op:
+    _require_cuda(x, out, gamma, beta)
+    assert x.dtype == torch.float32 and gamma.dtype == torch.float32
+    lib = _lib.load()
+    layc = lay.c
+    args = (x.data_ptr(), x.stride(0), out.data_ptr(), out.stride(0), dt_of(out), gamma.data_ptr(), beta.data_ptr(),
+            C.byref(layc), gamma.numel(), eps)
+    keep = (x, out, gamma, beta, lay, layc)
+    return lambda _k=keep: _lib.check(lib.cvb200_layernorm_seq(*args, _stream()), "layernorm_seq")
+
+
+def relpos_attention_op(qkv, pos, center: int, bias_u, bias_v, out, lay: SeqLayout, heads: int, scale: float,
+                        chunk: int = 0, flops: int = 0) -> Op:
+    """qkv fp32 [rows, 3*heads*64]; pos fp32 [n_rel, heads*64] with PE(r) projected at row center - r."""
+    _require_cuda(qkv, pos, bias_u, bias_v, out)
+    assert qkv.dtype == torch.float32 and pos.dtype == torch.float32 and bias_u.dtype == torch.float32
+    assert bias_u.is_contiguous() and bias_v.is_contiguous() and pos.stride(1) == 1
+    lib = _lib.load()
+    layc = lay.c
+    args = (qkv.data_ptr(), qkv.stride(0), pos.data_ptr(), pos.stride(0), center, pos.shape[0], bias_u.data_ptr(),
+            bias_v.data_ptr(), out.data_ptr(), out.stride(0), dt_of(out), C.byref(layc), heads, scale, chunk)
+    keep = (qkv, pos, bias_u, bias_v, out, lay, layc)
+    return _profiled("relpos_attention", flops,
+                     lambda _k=keep: _lib.check(lib.cvb200_relpos_attention(*args, _stream()), "relpos_attention"))
+
+
+def groupnorm1_mish_op(h, out, gamma, beta, lay: SeqLayout, eps: float = 1e-5) -> Op:
+    _require_cuda(h, out, gamma, beta)
+    assert h.dtype == torch.float32
+    lib = _lib.load()
+    layc = lay.c
+    args = (h.data_ptr(), h.stride(0), out.data_ptr(), out.stride(0), dt_of(out), gamma.data_ptr(), beta.data_ptr(),
+            gamma.numel(), C.byref(layc), eps)
+    keep = (h, out, gamma, beta, lay, layc)
+    return lambda _k=keep: _lib.check(lib.cvb200_groupnorm1_mish(*args, _stream()), "groupnorm1_mish")
+
+
+def interp_rows_op(x, src_lay: SeqLayout, out, dst_lay: SeqLayout, segs: torch.Tensor, C_: int) -> Op:
+    """segs int32 [n_seq, 4, 4] = (src_start, src_len, dst_start, dst_len) (flow/length_regulator.py:52-70)."""
+    _require_cuda(x, out, segs)
+    assert x.dtype == torch.float32 and segs.dtype == torch.int32 and segs.is_contiguous()
+    assert tuple(segs.shape) == (src_lay.n_seq, 4, 4)
+    lib = _lib.load()
+    sc, dc = src_lay.c, dst_lay.c
+    args = (x.data_ptr(), x.stride(0), C.byref(sc), out.data_ptr(), out.stride(0), dt_of(out), C.byref(dc), segs.data_ptr(), C_)
+    keep = (x, out, segs, src_lay, dst_lay, sc, dc)
+    return lambda _k=keep: _lib.check(lib.cvb200_interp_rows(*args, _stream()), "interp_rows")
+
+
+def l2_normalize(x: torch.Tensor, out: torch.Tensor):
+    _require_cuda(x, out)
+    assert x.dtype == torch.float32 and out.dtype == torch.float32 and x.is_contiguous() and out.is_contiguous()
+    _lib.check(_lib.load().cvb200_l2_normalize(x.data_ptr(), out.data_ptr(), x.shape[0], x.shape[1], _stream()), "l2_normalize")

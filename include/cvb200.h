@@ -246,6 +246,42 @@ int cvb200_nct_to_rows(const float* src, int64_t seq_stride, int64_t c_stride, i
 int cvb200_rows_to_nct(const float* src, int lds, int C, float* out, int64_t seq_stride, int64_t c_stride,
                        const cvb200_layout* lay, void* stream);
 
+/* ---- flow front-end: what flow.inference does before the CFM ---- */
+
+/* nn.Embedding gather: out[row] = table[clamp(token, 0, vocab-1)] on valid rows, 0 elsewhere.
+ * flow/flow.py:131-135 (input_embedding(torch.clamp(token, min=0)) * mask), :288-290.  tokens int32 [n_seq][tok_ld]
+ * (token t of sequence b at tokens[b*tok_ld + t]); table fp32 [vocab][C]. */
+int cvb200_embed_tokens(const int32_t* tokens, int tok_ld, const float* table, int vocab, int C, void* out, int ldo, int out_dt,
+                        const cvb200_layout* lay, void* stream);
+
+/* LayerNorm(C = 256 | 512) per valid row of a varlen layout, zeros on the invalid rows (they are the next conv's padding):
+ * transformer/subsampling.py:83-86 (eps 1e-5), transformer/encoder_layer.py:145-146 (eps 1e-12), transformer/encoder.py:104. */
+int cvb200_layernorm_seq(const float* x, int ldx, void* out, int ldo, int out_dt, const float* gamma, const float* beta,
+                         const cvb200_layout* lay, int C, float eps, void* stream);
+
+/* RelPositionMultiHeadedAttention core, transformer/attention.py:243-330 (ESPnet rel-pos, rel_shift as an index):
+ *   s[i,j] = ((q_i + u_h) . k_j + (q_i + v_h) . pos[center - (i - j)][h]) * scale,  out = softmax_j(s) V,
+ *   key j visible iff j < len and (chunk == 0 or j < (i / chunk + 1) * chunk)   (utils/mask.py:116-124,191-197).
+ * qkv fp32 [rows, ld] = [Q(heads*64) | K | V] per row; pos fp32 [n_rel, ldp] = linear_pos(PE(r)) at row center - r
+ * (transformer/embedding.py:224-254); bias_u / bias_v fp32 [heads*64]; out [rows, ldo] fp32 or bf16. */
+int cvb200_relpos_attention(const float* qkv, int ld, const float* pos, int ldp, int center, int n_rel, const float* bias_u,
+                            const float* bias_v, void* out, int ldo, int out_dt, const cvb200_layout* lay, int heads,
+                            float scale, int chunk, void* stream);
+
+/* GroupNorm(1, C) + Mish over each utterance (statistics over C channels x valid frames), zeros on invalid rows:
+ * flow/length_regulator.py:33-38. */
+int cvb200_groupnorm1_mish(const float* h, int ldh, void* out, int ldo, int out_dt, const float* gamma, const float* beta,
+                           int C, const cvb200_layout* lay, float eps, void* stream);
+
+/* InterpolateRegulator.inference's piecewise F.interpolate(mode='linear') (flow/length_regulator.py:52-70) on time-major
+ * rows: segs int32 [n_seq][4][4] = (src_start, src_len, dst_start, dst_len) per piece, dst_len = 0 for an unused piece;
+ * x fp32 rows in src_lay (token rate) -> out rows in dst_lay (mel rate). */
+int cvb200_interp_rows(const float* x, int ldx, const cvb200_layout* src_lay, void* out, int ldo, int out_dt,
+                       const cvb200_layout* dst_lay, const int32_t* segs, int C, void* stream);
+
+/* F.normalize(x, dim=1) of the speaker embedding (flow/flow.py:127): x [S][K] -> x / max(||x||_2, 1e-12). */
+int cvb200_l2_normalize(const float* x, float* out, int S, int K, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
