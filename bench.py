@@ -24,7 +24,24 @@ if ROOT not in sys.path:
 import torch
 
 PROMPT_FRAMES, GEN_FRAMES, HOP, SR = 281, 937, 256, 24000      # 3 s prompt + 10 s generated
-WORKLOAD = "CosyVoice-300M flow (ConditionalCFM, 10 Euler steps, CFG) + HiFT, batch {b} synthetic 10 s utterances (3 s prompt)"
+PROMPT_TOKENS, GEN_TOKENS = 75, 250                             # 25 tokens/s: int(250 / 25 * 24000 / 256) = 937 frames
+WORKLOAD = ("CosyVoice-300M flow.inference (token embedding + Conformer encoder + length regulator + ConditionalCFM, "
+            "10 Euler steps, CFG) + HiFT, batch {b} synthetic 10 s utterances (3 s prompt), from speech tokens")
+
+
+def utterance_inputs(n: int, first_index: int = 0):
+    """SURVEY.md 8d synthetic inputs, seed 1234+u per utterance index u (noise 4321+u): speech tokens, prompt tokens,
+    prompt mel [1, 281, 80], speaker embedding [1, 512], CFM noise [1, 80, 1218]."""
+    from cosyvoice_b200 import synthetic
+    toks, ptoks, pfeats, embs, zs = [], [], [], [], []
+    for i in range(n):
+        u = first_index + i
+        t, pt, pf, e = synthetic.frontend_inputs(False, GEN_TOKENS, PROMPT_TOKENS, seed=1234 + u, sample_rate=SR)
+        assert pf.shape[1] == PROMPT_FRAMES
+        g = torch.Generator().manual_seed(4321 + u)
+        toks.append(t), ptoks.append(pt), pfeats.append(pf), embs.append(e)
+        zs.append(torch.randn(1, 80, PROMPT_FRAMES + GEN_FRAMES, generator=g))
+    return toks, ptoks, pfeats, embs, zs
 
 
 def peaks():
@@ -89,15 +106,16 @@ def cpu_reference_pass(n_timesteps: int = 10):
     restatement of the reference's PyTorch modules pinned to the reference's outputs by tests/golden).
     /root/reference itself (Python + uninstallable deps) cannot travel to the GPU box, hence kind = "port"."""
     from cosyvoice_b200 import synthetic
-    from oracle import flow_ref, hift_ref
+    from oracle import encoder_ref, flow_ref, hift_ref
     fsd, hsd = synthetic.flow_estimator_sd(False, seed=0), synthetic.hift_sd(False, seed=1)
-    mus, spks, conds, zs = synthetic.flow_inputs(1, GEN_FRAMES, PROMPT_FRAMES)
-    T = mus[0].shape[-1]
+    esd = synthetic.flow_frontend_sd(False, seed=2)
+    toks, ptoks, pfeats, embs, zs = utterance_inputs(1)
+    T = PROMPT_FRAMES + GEN_FRAMES
 
     def run():
         with torch.inference_mode():
-            mel = flow_ref.solve_euler(fsd, zs[0], flow_ref.cosine_t_span(n_timesteps), mus[0], torch.ones(1, 1, T),
-                                       spks[0], conds[0])
+            mu, spks, cond, _, _ = encoder_ref.frontend_v1(esd, toks[0], ptoks[0], pfeats[0], embs[0], sample_rate=SR)
+            mel = flow_ref.solve_euler(fsd, zs[0], flow_ref.cosine_t_span(n_timesteps), mu, torch.ones(1, 1, T), spks, cond)
             gen = mel[:, :, PROMPT_FRAMES:]
             pv, nz = hift_ref.draw_source_rng(1, gen.shape[-1] * HOP)
             wav, _ = hift_ref.hift_inference(hsd, gen, pv, nz)
@@ -120,7 +138,8 @@ def run_reference(args):
         run()
     dt = (time.perf_counter() - t0) / args.steps
     val = audio_seconds(1) / dt
-    sample = "1 of the batch's utterances per step (T=1218 frames, 10 Euler steps + HiFT), fp32, flush_denormal on"
+    sample = ("1 of the batch's utterances per step (325 tokens -> T=1218 frames: front-end, 10 Euler steps, HiFT), fp32, "
+              "flush_denormal on")
     print(json.dumps({
         "impl": "reference", "metric": "audio_seconds_per_second", "value": val, "unit": "audio-s/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak",
@@ -147,10 +166,9 @@ def run_ours(args):
         dist.init_process_group("nccl", device_id=dev)
     B, K, W = args.batch, args.steps, max(args.warmup, 1)
     be = AcousticBackend(synthetic.flow_estimator_sd(False, seed=0), synthetic.hift_sd(False, seed=1), v2=False,
-                         dtype=torch.bfloat16, device=dev)
+                         dtype=torch.bfloat16, device=dev, frontend_sd=synthetic.flow_frontend_sd(False, seed=2))
     # utterances are independent: rank r owns utterances [r*B, (r+1)*B) -- no collective on the data path
-    mus, spks, conds, zs = synthetic.flow_inputs(B, GEN_FRAMES, PROMPT_FRAMES, first_index=rank * B)
-    prompt_lens = [PROMPT_FRAMES] * B
+    toks, ptoks, pfeats, embs, zs = utterance_inputs(B, first_index=rank * B)
 
     def barrier():
         torch.cuda.synchronize()
@@ -172,7 +190,7 @@ def run_ours(args):
         return ms.item() / k
 
     # ---- resident leg (value)
-    res = be.prepare_resident(mus, spks, conds, zs, prompt_lens)
+    res = be.prepare_resident_tokens(toks, ptoks, pfeats, embs, zs, sample_rate=SR)
     for _ in range(W):
         be.step_resident(res)
     sampler = ClockSampler(local)
@@ -191,21 +209,22 @@ def run_ours(args):
         res["st"]["x"].copy_(res["z_rows"])
         be.cfm.solve_rows(res["lay1"], 10)
     ms_flow = timed(flow_only, max(1, K // 2))
+    ms_front = timed(res["fprog"].run, max(1, K // 2))
 
     # ---- e2e leg: public batched API, pinned host inputs, H2D + D2H inside the timed region
     pin = lambda seq: [a.contiguous().pin_memory() for a in seq]
-    h_mus, h_spks, h_conds, h_zs = pin(mus), pin(spks), pin(conds), pin(zs)
+    h_toks, h_ptoks, h_pfeats, h_embs, h_zs = pin(toks), pin(ptoks), pin(pfeats), pin(embs), pin(zs)
     L = GEN_FRAMES * HOP
     h_out = torch.empty(B, L, dtype=torch.float32).pin_memory()
 
     def e2e_step():
-        wavs = be.synthesize_batch(h_mus, h_spks, h_conds, h_zs, prompt_lens)
+        wavs = be.synthesize_tokens_batch(h_toks, h_ptoks, h_pfeats, h_embs, h_zs, sample_rate=SR)
         for b, w in enumerate(wavs):
             h_out[b].copy_(w[0], non_blocking=True)
         torch.cuda.current_stream().synchronize()
     e2e_step()
     ms_e2e = timed(e2e_step, max(1, K // 2))
-    h2d = sum(a.numel() * 4 for seq in (h_mus, h_spks, h_conds, h_zs) for a in seq)
+    h2d = sum(a.numel() * 4 for seq in (h_toks, h_ptoks, h_pfeats, h_embs, h_zs) for a in seq)
     d2h = h_out.numel() * 4
 
     # ---- roofline leg: one eager (non-graph) step with CUDA events around every GEMM / attention launch
@@ -236,7 +255,7 @@ def run_ours(args):
     tc = prof.get("tapgemm_tc", dict(launches=0, flops=0, ms=1e-9))
     achieved = tc["flops"] / (tc["ms"] * 1e-3) / 1e12
     att = prof.get("attention", dict(launches=0, flops=0, ms=1e-9))
-    total_flops = res["hprog"].flops + 10 * be.cfm.estimator.program(res["lay1"].paired()).flops
+    total_flops = res["hprog"].flops + 10 * be.cfm.estimator.program(res["lay1"].paired()).flops + res["fprog"].flops
     # DRAM bytes per launch of the dominant kernel from the committed ncu capture (profiles/, `ncu --metrics
     # dram__bytes_read.sum,dram__bytes_write.sum` over the GEMM launches of two estimator calls of this workload)
     traffic, traffic_src = None, None
@@ -253,7 +272,8 @@ def run_ours(args):
         "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
         "config": {"workload": WORKLOAD.format(b=B), "global_batch": world * B, "parallelism": f"utterance-sharded x{world}",
                    "l2": "inputs_larger_than_L2 (multi-GB activation working set per step)",
-                   "ms_per_cfm_step": ms_flow / 10.0, "flow_ms": ms_flow, "algorithmic_tflop_per_step": total_flops / 1e12,
+                   "ms_per_cfm_step": ms_flow / 10.0, "flow_ms": ms_flow, "frontend_ms": ms_front,
+                   "frontend_tflop": res["fprog"].flops / 1e12, "algorithmic_tflop_per_step": total_flops / 1e12,
                    "end_to_end_frac_of_bf16_peak": total_flops / (ms_step * 1e-3) / 1e12 / pk["tflops"]},
         "e2e": {"value": world * audio_seconds(B) / (ms_e2e * 1e-3), "unit": "audio-s/s", "h2d_bytes_per_step": h2d,
                 "d2h_bytes_per_step": d2h, "ms_per_step": ms_e2e},
@@ -278,8 +298,8 @@ def run_ours(args):
         run()
         dt = time.perf_counter() - t0
         out["cpu_baseline"] = {"value": audio_seconds(1) / dt, "unit": "audio-s/s", "cores": cores, "kind": "port",
-                               "sample": "1 utterance of the batch (T=1218, 10 Euler steps + HiFT), single cold run, fp32, "
-                                         "flush_denormal on"}
+                               "sample": "1 utterance of the batch (325 tokens -> T=1218: front-end, 10 Euler steps, HiFT), "
+                                         "single cold run, fp32, flush_denormal on"}
     print(json.dumps(out))
     if world > 1:
         dist.destroy_process_group()

@@ -172,6 +172,7 @@ class _Program:
         self.f = z(Rmax, FF)
         self.mu = z(mel.rows, N_FEATS, dtype=torch.float32)
         self.ops: List[ops.Op] = []
+        self.flops = 0          # algorithmic FLOPs of one run at the lengths of construction (bench.py)
         g = self._gemm
         X, n = self.X[:Rt], self.n[:Rt]
         # ---- token embedding + LinearNoSubsampling (flow.py:131-135, subsampling.py:105-107)
@@ -214,7 +215,9 @@ class _Program:
             g(w.reg_out, cur, mel, self.mu)
 
     def _gemm(self, plan: TapPlan, A, L: SeqLayout, out0, **kw):
-        self.ops.append(ops.gemm_op(plan, A, L, out0, engine=self.engine, **kw))
+        fl = plan.flops_per_row * sum(L.lens)
+        self.ops.append(ops.gemm_op(plan, A, L, out0, engine=self.engine, flops=fl, **kw))
+        self.flops += fl
 
     def _layers(self, layers: List[_LayerW], pos: List[torch.Tensor], L: SeqLayout, R: int, chunk: int, copy_last: bool):
         """ConformerEncoderLayer x len(layers) (encoder_layer.py:191-236; macaron/cnn off, pre-norm eps 1e-12)."""
@@ -222,7 +225,10 @@ class _Program:
         for i, (lw, P) in enumerate(zip(layers, pos)):
             self.ops.append(ops.layernorm_seq_op(X, n, lw.ln_mha[0], lw.ln_mha[1], L, 1e-12))
             self._gemm(lw.qkv, n, L, qkv)
-            self.ops.append(ops.relpos_attention_op(qkv, P, self.center, lw.u, lw.v, o, L, HEADS, 1.0 / math.sqrt(D_K), chunk))
+            fl = sum(6 * HEADS * D_K * l * l for l in L.lens)        # (q+u).k, (q+v).p and p.v
+            self.ops.append(ops.relpos_attention_op(qkv, P, self.center, lw.u, lw.v, o, L, HEADS, 1.0 / math.sqrt(D_K), chunk,
+                                                    flops=fl))
+            self.flops += fl
             self._gemm(lw.out, o, L, X, res=X)
             self.ops.append(ops.layernorm_seq_op(X, n, lw.ln_ff[0], lw.ln_ff[1], L, 1e-12))
             self._gemm(lw.ff1, n, L, f, act=_lib.ACT_SILU)

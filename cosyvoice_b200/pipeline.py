@@ -1,6 +1,6 @@
-"""Flow decoder + HiFT vocoder as one batched call: the part of CosyVoiceModel.token2wav
-(cosyvoice/cli/model.py:130-175) that lies inside the hot path -- `flow.decoder(...)` on the encoder
-output followed by `hift.inference(...)` on the generated frames -- for a batch of independent utterances.
+"""Flow + HiFT vocoder as one batched call: the part of CosyVoiceModel.token2wav (cosyvoice/cli/model.py:130-175) that
+lies inside the hot path -- `flow.inference(...)` (front-end + CFM; or `flow.decoder(...)` alone on a given encoder output)
+followed by `hift.inference(...)` on the generated frames -- for a batch of independent utterances.
 """
 from typing import List, Optional, Sequence
 
@@ -13,11 +13,20 @@ from .hift import B200HiFTGenerator
 
 class AcousticBackend:
     def __init__(self, flow_sd, hift_sd, v2: bool = False, dtype: torch.dtype = torch.bfloat16, device="cuda",
-                 hift_dtype: Optional[torch.dtype] = None):
+                 hift_dtype: Optional[torch.dtype] = None, frontend_sd=None):
+        """flow_sd: estimator parameters (`decoder.estimator.*` stripped); frontend_sd: the rest of the flow module
+        (embedding, encoder, length regulator, speaker projection) -- enables the token entry points."""
         self.device = torch.device(device)
         self.v2 = v2
-        est = B200Estimator(flow_sd, causal=v2, dtype=dtype, device=device)
-        self.cfm = (B200CausalConditionalCFM if v2 else B200ConditionalCFM)(est)
+        if frontend_sd is not None:
+            from .frontend import B200CausalMaskedDiffWithXvec, B200MaskedDiffWithXvec
+            cls = B200CausalMaskedDiffWithXvec if v2 else B200MaskedDiffWithXvec
+            self.flow = cls(frontend_sd, dtype=dtype, device=device, estimator_state_dict=flow_sd)
+            self.cfm = self.flow.decoder
+        else:
+            self.flow = None
+            est = B200Estimator(flow_sd, causal=v2, dtype=dtype, device=device)
+            self.cfm = (B200CausalConditionalCFM if v2 else B200ConditionalCFM)(est)
         self.hift = B200HiFTGenerator(hift_sd, v2=v2, dtype=hift_dtype or dtype, device=device)
         self.sample_rate = 24000
 
@@ -30,6 +39,46 @@ class AcousticBackend:
         gen = [m[:, :, p:] for m, p in zip(mels, prompt_lens)]
         wavs, _ = self.hift.inference_batch(gen, uniform_stride=True)
         return wavs
+
+    @torch.inference_mode()
+    def synthesize_tokens_batch(self, tokens: Sequence[torch.Tensor], prompt_tokens: Sequence[torch.Tensor],
+                                prompt_feats: Sequence[torch.Tensor], embeddings: Sequence[torch.Tensor],
+                                zs: Optional[Sequence[torch.Tensor]] = None, n_timesteps: int = 10,
+                                sample_rate: Optional[int] = None) -> List[torch.Tensor]:
+        """The whole back-end from speech tokens (host or device): flow.inference (front-end + CFM) per utterance, then
+        hift.inference on the generated frames (cli/model.py:137-161).  Returns waveforms [1, L_u] on device."""
+        if self.flow is None:
+            raise RuntimeError("AcousticBackend was built without frontend_sd")
+        gen = self.flow.inference_batch(tokens, prompt_tokens, prompt_feats, embeddings, zs, n_timesteps,
+                                        sample_rate or self.sample_rate)
+        wavs, _ = self.hift.inference_batch(gen, uniform_stride=True)
+        return wavs
+
+    def prepare_resident_tokens(self, tokens, prompt_tokens, prompt_feats, embeddings, zs, sample_rate: Optional[int] = None):
+        """Resident state for step_resident with the front-end inside the step: tokens, prompt mels, speaker vectors and
+        noise are copied to HBM here, once."""
+        sr = sample_rate or self.sample_rate
+        f, dev = self.flow, self.device
+        B = len(tokens)
+        n_prompt = [int(p.numel()) for p in prompt_tokens]
+        mel_lens = [f._mel_lens(n_prompt[b], int(tokens[b].numel()), int(prompt_feats[b].shape[-2]), sr) for b in range(B)]
+        cat = [torch.cat([prompt_tokens[b].reshape(-1).to(torch.int32), tokens[b].reshape(-1).to(torch.int32)]) for b in range(B)]
+        fprog = f.encode_batch(cat, n_prompt, mel_lens, embeddings, sr)
+        lay1 = fprog.mel
+        lens = [a + b for a, b in mel_lens]
+        prog, st = self.cfm._state(lay1)
+        st["cond"].zero_()
+        z_rows = torch.zeros_like(st["x"])
+        for b in range(B):
+            r0, l1 = lay1.row0[b], mel_lens[b][0]
+            st["cond"][r0:r0 + l1].copy_(prompt_feats[b].reshape(-1, N_FEATS)[:l1].to(dev, torch.float32))
+            z_rows[r0:r0 + lens[b]].copy_(zs[b].reshape(N_FEATS, lens[b]).to(dev, torch.float32).t())
+        prompt_lens = [m[0] for m in mel_lens]
+        gen_lens = [m[1] for m in mel_lens]
+        hprog = self.hift.program(gen_lens)
+        mel_nct = torch.zeros(B, N_FEATS, max(lens), dtype=torch.float32, device=dev)
+        return dict(lay1=lay1, st=st, z_rows=z_rows, lens=lens, prompt_lens=prompt_lens, gen_lens=gen_lens, hprog=hprog,
+                    mel_nct=mel_nct, same_prompt=len(set(prompt_lens)) == 1, fprog=fprog)
 
     # ---- device-resident variant used by bench.py's `value` leg ---------------------------------
     def prepare_resident(self, mus, spks, conds, zs, prompt_lens):
@@ -59,6 +108,10 @@ class AcousticBackend:
     def step_resident(self, r: dict, n_timesteps: int = 10):
         """One pass over the batch with every input already in HBM (noise, mu, cond, spks)."""
         st, lay1, hprog = r["st"], r["lay1"], r["hprog"]
+        if r.get("fprog") is not None:          # front-end inside the step: tokens -> mu, spks (flow/flow.py:126-141)
+            r["fprog"].run()
+            st["mu"].copy_(r["fprog"].mu)
+            st["spks"].copy_(r["fprog"].spks)
         st["x"].copy_(r["z_rows"])
         self.cfm.solve_rows(lay1, n_timesteps)
         ops.rows_to_nct(st["x"], r["mel_nct"], lay1)

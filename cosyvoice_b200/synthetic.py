@@ -295,7 +295,7 @@ def flow_frontend_sd(v2: bool, seed: int = 2) -> SD:
     return sd
 
 
-def frontend_inputs(v2: bool, n_tokens: int, n_prompt_tokens: int, seed: int):
+def frontend_inputs(v2: bool, n_tokens: int, n_prompt_tokens: int, seed: int, sample_rate: int = 22050):
     """token / prompt_token int32 [1, n], prompt_feat [1, T_p, 80] time-major log-mel-like, embedding [1, spk].
     T_p = the reference's own prompt ratio: v1 3.75 frames per token at 22.05 kHz/256 -> int(n / 25 * 22050 / 256);
     v2 2 frames per token."""
@@ -303,7 +303,7 @@ def frontend_inputs(v2: bool, n_tokens: int, n_prompt_tokens: int, seed: int):
     V, SPK = (6561, 192) if v2 else (4096, 512)
     token = torch.randint(0, V, (1, n_tokens), generator=g, dtype=torch.int32)
     prompt_token = torch.randint(0, V, (1, n_prompt_tokens), generator=g, dtype=torch.int32)
-    t_p = 2 * n_prompt_tokens if v2 else int(n_prompt_tokens / 25 * 22050 / 256)
+    t_p = 2 * n_prompt_tokens if v2 else int(n_prompt_tokens / 25 * sample_rate / 256)
     prompt_feat = torch.randn(1, t_p, 80, generator=g) * 2 - 4
     embedding = torch.randn(1, SPK, generator=g)
     return token, prompt_token, prompt_feat, embedding

@@ -225,3 +225,35 @@ def test_frontend_needs_cuda_and_b1():
     d = dict(init_weights.flow_frontend_sd(False, seed=2))
     with pytest.raises(RuntimeError):
         B200MaskedDiffWithXvec(d, device="cpu", estimator_state_dict=init_weights.flow_estimator_sd(False))
+
+
+def test_cosyvoice2_session_streams_through_the_whole_cuda_back_end(golden_dir):
+    """CosyVoice2Model.token2wav's bookkeeping (cli/model.py:334-366) over the REAL B200 flow (front-end + CFM, chunk-masked
+    encoder as cli/model.py:314 sets it) and the B200 HiFT: chunk lengths, caches on the device, finite bounded audio;
+    the last (finalize) chunk's mel equals a one-shot flow.inference of the same tokens."""
+    from cosyvoice_b200.hift import B200HiFTGenerator
+    from cosyvoice_b200.token2wav import Token2Wav2
+    from oracle import token2wav_ref as T
+    d = _load(golden_dir, "frontend_v2.pt")
+    flow = _flow(True, torch.bfloat16, d)
+    hift = B200HiFTGenerator(init_weights.hift_sd(True, seed=1), v2=True, dtype=torch.bfloat16, device=DEV)
+    m = Token2Wav2(flow, hift, device=DEV)
+    flow.encoder.static_chunk_size = 2 * flow.input_frame_rate                     # model.py:314
+    m.open_session("u")
+    g = torch.Generator().manual_seed(11)
+    tok = torch.randint(0, 6561, (1, 70), generator=g, dtype=torch.int32)
+    pt = torch.randint(0, 6561, (1, 9), generator=g, dtype=torch.int32)
+    pf, emb = torch.randn(1, 18, 80, generator=g) * 2 - 4, torch.randn(1, 192, generator=g)
+    total = 0
+    for n, off, fin in T.SCENARIO_V2["steps"]:
+        wav = m.token2wav(tok[:, :n], pt, pf, emb, "u", off, finalize=fin)
+        assert wav.is_cuda and torch.isfinite(wav).all() and wav.abs().max() <= 0.99 + 1e-6
+        cached = 0 if off == 0 else 8
+        assert wav.shape[1] == ((n - off) * 2 + cached) * 480 - (0 if fin else 3840)
+        total += wav.shape[1]
+    assert total == 70 * 2 * 480
+    m.close_session("u")
+    i32 = lambda k: torch.tensor([k], dtype=torch.int32)
+    mel, _ = flow.inference(token=tok.to(DEV), token_len=i32(70), prompt_token=pt.to(DEV), prompt_token_len=i32(9),
+                            prompt_feat=pf.to(DEV), prompt_feat_len=i32(18), embedding=emb.to(DEV))
+    assert mel.shape == (1, 80, 140) and torch.isfinite(mel).all()
