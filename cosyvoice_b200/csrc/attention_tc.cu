@@ -31,7 +31,7 @@ namespace {
 constexpr int HD = 64, BQ = 128, BK = 128;
 constexpr int TILE_BYTES = 128 * 64 * 2;            // 16 KiB
 constexpr int KV_STAGES = 2;
-constexpr int SMEM_BYTES = 1024 + TILE_BYTES * (1 + 2 * KV_STAGES) + 128 + 2 * 2 * 128 * 4;   // barriers + smax
+constexpr int SMEM_BYTES = 1024 + TILE_BYTES * (1 + 2 * KV_STAGES) + 256 + 2 * 2 * 128 * 4;   // barriers + smax
 constexpr int TM_S = 0, TM_P = 128, TM_O = 192, TM_COLS = 256;
 
 // MN-major 128B-swizzled shared-memory operand (V tile: rows = keys (K dim), 64 d (N dim) contiguous = 128 B).
@@ -51,6 +51,27 @@ __device__ __forceinline__ float ex2_approx(float x) {
   asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
   return y;
 }
+
+// exp2 on the FMA/ALU pipes (Cody-Waite split + degree-3 minimax polynomial of 2^f on [-0.5, 0.5], relative error
+// 7.5e-5, far below the bf16 rounding of P) for every ATTN_POLY_EVERY-th pair of probabilities.  x <= RESCALE_LOG2;
+// -inf (masked key) gives 2^-126.  MEASURED SLOWER and therefore OFF by default (profiles/r01_attn_ab.txt: T = 609
+// 401 TFLOP/s without, 394 / 392 / 372 with every 4th / 3rd / 2nd pair): the MUFU pipe is the busiest unit (ncu 54 %)
+// but not the limiter -- the per-block chain S -> max -> exp -> P -> PV of a CTA is latency bound, and the extra
+// FMA/ALU instructions lengthen it.
+#ifndef ATTN_POLY_EVERY
+#define ATTN_POLY_EVERY 0
+#endif
+__device__ __forceinline__ float ex2_poly(float x) {
+  x = fmaxf(x, -126.f);
+  const float t = x + 12582912.f;                 // 1.5 * 2^23: the integer part lands in the low mantissa bits
+  const float f = x - (t - 12582912.f);
+  const float p = fmaf(fmaf(fmaf(0.05517164617776871f, f, 0.2426111251115799f), f, 0.6932609677314758f), f, 0.9999280571937561f);
+  return __int_as_float(__float_as_int(p) + (__float_as_int(t) << 23));
+}
+// O is rescaled only when a row's running max has grown by more than 2^RESCALE_LOG2 since the offset in use was
+// chosen (probabilities then stay below 2^8, exact in fp32 sums and harmless in bf16): with random scores the max
+// moves in almost every early block, so the unconditional variant paid a TMEM round trip of O per block.
+constexpr float RESCALE_LOG2 = 8.f;
 
 __device__ __forceinline__ uint32_t pack2(float lo, float hi) {
   __nv_bfloat162 t = __floats2bfloat162_rn(lo, hi);
@@ -90,21 +111,26 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tm, __nv_bfloat16* __res
   uint8_t* sV = sK + KV_STAGES * TILE_BYTES;               // [KV_STAGES]
   uint64_t* bars = reinterpret_cast<uint64_t*>(sV + KV_STAGES * TILE_BYTES);
   uint64_t* q_full = bars;                                 // 1
-  uint64_t* kv_full = bars + 1;                            // [2]
-  uint64_t* kv_empty = bars + 3;                           // [2]
-  uint64_t* s_full = bars + 5;
-  uint64_t* s_free = bars + 6;
-  uint64_t* p_full = bars + 7;
-  uint64_t* pv_done = bars + 8;
-  uint64_t* q_free = bars + 9;                             // every QK^T of the item has retired: Q may be overwritten
-  uint64_t* o_free = bars + 10;                            // the item's O has been read out (256 arrivals)
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 11);
-  float* smax = reinterpret_cast<float*>(bars + 12);      // [2 parities][2 halves][128 rows]
+  uint64_t* k_full = bars + 1;                             // [2]  K and V run on separate rings: a K stage is free as soon
+  uint64_t* k_empty = bars + 3;                            // [2]  as its QK^T has retired, a V stage only after its PV
+  uint64_t* v_full = bars + 5;                             // [2]
+  uint64_t* v_empty = bars + 7;                            // [2]
+  uint64_t* s_full = bars + 9;
+  uint64_t* s_free = bars + 10;
+  uint64_t* p_full = bars + 11;
+  uint64_t* pv_done = bars + 12;
+  uint64_t* q_free = bars + 13;                            // every QK^T of the item has retired: Q may be overwritten
+  uint64_t* o_free = bars + 14;                            // the item's O has been read out (256 arrivals)
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 15);
+  float* smax = reinterpret_cast<float*>(bars + 32);      // [2 parities][2 halves][128 rows]
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   if (threadIdx.x == 0) {
     ptx::mbar_init(q_full, 1);
-    for (int i = 0; i < KV_STAGES; ++i) { ptx::mbar_init(&kv_full[i], 1); ptx::mbar_init(&kv_empty[i], 1); }
+    for (int i = 0; i < KV_STAGES; ++i) {
+      ptx::mbar_init(&k_full[i], 1); ptx::mbar_init(&k_empty[i], 1);
+      ptx::mbar_init(&v_full[i], 1); ptx::mbar_init(&v_empty[i], 1);
+    }
     ptx::mbar_init(s_full, 1);
     ptx::mbar_init(s_free, 256);
     ptx::mbar_init(p_full, 256);
@@ -124,21 +150,48 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tm, __nv_bfloat16* __res
 
   if (warp == 0) {
     if (lane == 0) {
-      uint32_t n = 0, g = 0;
-      for (int it = blockIdx.x; it < n_items; it += gridDim.x) {
-        const AttnItem w = attn_item(lay, it, heads);
-        if (!w.valid) continue;
-        if (n > 0) ptx::mbar_wait(q_free, (n - 1) & 1);
-        ptx::mbar_arrive_expect_tx(q_full, TILE_BYTES);
-        ptx::tma_load_2d(sQ, &tm, q_full, w.head * HD, w.seq0 + w.q0);
-        for (int j = 0; j < w.nblk; ++j, ++g) {
-          const int st = g % KV_STAGES;
-          ptx::mbar_wait(&kv_empty[st], ((g / KV_STAGES) & 1) ^ 1);
-          ptx::mbar_arrive_expect_tx(&kv_full[st], 2 * TILE_BYTES);
-          ptx::tma_load_2d(sK + st * TILE_BYTES, &tm, &kv_full[st], inner + w.head * HD, w.seq0 + j * BK);
-          ptx::tma_load_2d(sV + st * TILE_BYTES, &tm, &kv_full[st], 2 * inner + w.head * HD, w.seq0 + j * BK);
+      // Two cursors over the same flattened (item, key block) sequence: the K stream (which also brings each item's Q
+      // tile) runs one block ahead of the V stream.  K(g+1)'s stage frees when QK(g-1) retires, which precedes the
+      // retirement of PV(g-2) that frees V(g)'s stage (the MMA thread issues QK(g+1) before PV(g)), so the single
+      // producer thread never waits on the later event first.
+      struct Cur { int it, j; uint32_t g, n; AttnItem w; bool ok; };
+      auto seek = [&](Cur& c) {
+        for (; c.it < n_items; c.it += gridDim.x) {
+          c.w = attn_item(lay, c.it, heads);
+          if (c.w.valid) { c.ok = true; return; }
         }
-        ++n;
+        c.ok = false;
+      };
+      auto adv = [&](Cur& c) {
+        ++c.g;
+        if (++c.j == c.w.nblk) { c.j = 0; ++c.n; c.it += gridDim.x; seek(c); }
+      };
+      auto load_k = [&](const Cur& c) {
+        if (c.j == 0) {
+          if (c.n > 0) ptx::mbar_wait(q_free, (c.n - 1) & 1);
+          ptx::mbar_arrive_expect_tx(q_full, TILE_BYTES);
+          ptx::tma_load_2d(sQ, &tm, q_full, c.w.head * HD, c.w.seq0 + c.w.q0);
+        }
+        const int st = c.g % KV_STAGES;
+        ptx::mbar_wait(&k_empty[st], ((c.g / KV_STAGES) & 1) ^ 1);
+        ptx::mbar_arrive_expect_tx(&k_full[st], TILE_BYTES);
+        ptx::tma_load_2d(sK + st * TILE_BYTES, &tm, &k_full[st], inner + c.w.head * HD, c.w.seq0 + c.j * BK);
+      };
+      auto load_v = [&](const Cur& c) {
+        const int st = c.g % KV_STAGES;
+        ptx::mbar_wait(&v_empty[st], ((c.g / KV_STAGES) & 1) ^ 1);
+        ptx::mbar_arrive_expect_tx(&v_full[st], TILE_BYTES);
+        ptx::tma_load_2d(sV + st * TILE_BYTES, &tm, &v_full[st], 2 * inner + c.w.head * HD, c.w.seq0 + c.j * BK);
+      };
+      Cur kc;
+      kc.it = blockIdx.x; kc.j = 0; kc.g = 0; kc.n = 0; kc.ok = false;
+      seek(kc);
+      Cur vc = kc;
+      if (kc.ok) { load_k(kc); adv(kc); }
+      while (vc.ok) {
+        if (kc.ok) { load_k(kc); adv(kc); }
+        load_v(vc);
+        adv(vc);
       }
     }
   } else if (warp == 1) {
@@ -148,7 +201,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tm, __nv_bfloat16* __res
       const uint32_t q_base = ptx::smem_u32(sQ);
       auto issue_qk = [&](uint32_t gg) {
         const int st = gg % KV_STAGES;
-        ptx::mbar_wait(&kv_full[st], (gg / KV_STAGES) & 1);
+        ptx::mbar_wait(&k_full[st], (gg / KV_STAGES) & 1);
         if (gg > 0) ptx::mbar_wait(s_free, (gg - 1) & 1);     // softmax has pulled S(g-1) out of TMEM
         ptx::tc_fence_after();
         const uint32_t k_base = ptx::smem_u32(sK + st * TILE_BYTES);
@@ -156,6 +209,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tm, __nv_bfloat16* __res
         for (int k = 0; k < HD / 16; ++k)
           ptx::umma_ss(tmem + TM_S, ptx::make_sw128_kmajor_desc(q_base + k * 32), ptx::make_sw128_kmajor_desc(k_base + k * 32),
                        idesc_qk, k != 0);
+        ptx::umma_commit(&k_empty[st]);                       // the K stage is dead once this QK^T has retired
         ptx::umma_commit(s_full);
       };
       uint32_t n = 0, g = 0;
@@ -170,12 +224,13 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tm, __nv_bfloat16* __res
           const int st = g % KV_STAGES;
           ptx::mbar_wait(p_full, g & 1);                       // P(g) is in TMEM, O has been rescaled
           if (j == 0 && n > 0) ptx::mbar_wait(o_free, (n - 1) & 1);   // previous item's O has been read out
+          ptx::mbar_wait(&v_full[st], (g / KV_STAGES) & 1);
           ptx::tc_fence_after();
           const uint32_t v_base = ptx::smem_u32(sV + st * TILE_BYTES);
 #pragma unroll
           for (int k = 0; k < BK / 16; ++k)
             ptx::umma_ts(tmem + TM_O, tmem + TM_P + k * 8, make_sw128_mnmajor_desc(v_base + k * 2048), idesc_pv, (j | k) != 0);
-          ptx::umma_commit(&kv_empty[st]);
+          ptx::umma_commit(&v_empty[st]);
           ptx::umma_commit(pv_done);
         }
         ++n;
@@ -195,7 +250,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tm, __nv_bfloat16* __res
       const AttnItem w = attn_item(lay, it, heads);
       if (!w.valid) continue;
       const int len = w.len;
-      float m_run = -INFINITY, l_half = 0.f;
+      float m_run = -INFINITY, m_use = -INFINITY, l_half = 0.f;   // running max; the max the exponent offset uses
       for (int j = 0; j < w.nblk; ++j, ++g) {
         ptx::mbar_wait(s_full, g & 1);
         ptx::tc_fence_after();
@@ -226,10 +281,15 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tm, __nv_bfloat16* __res
         xch[half * 128 + row] = m_loc;
         ptx::named_bar_sync(1, 256);
         const float m_new = fmaxf(m_run, fmaxf(m_loc, xch[(half ^ 1) * 128 + row]));
-        const float corr = ex2_approx((m_run - m_new) * scale_log2);   // first block: exp2(-inf) = 0
-        const bool moved = __any_sync(0xffffffffu, m_new > m_run);
+        const bool need = j == 0 || (m_new - m_use) * scale_log2 > RESCALE_LOG2;
+        float corr = 1.f;
+        if (need) {
+          corr = j == 0 ? 0.f : ex2_approx((m_use - m_new) * scale_log2);
+          m_use = m_new;
+        }
+        const bool moved = __any_sync(0xffffffffu, need);
         m_run = m_new;
-        const float moff = m_new * scale_log2;
+        const float moff = m_use * scale_log2;
         if (g > 0) ptx::mbar_wait(pv_done, (g - 1) & 1);               // PV(g-1) retired: P and O may be touched
         ptx::tc_fence_after();
         float ls4[4] = {0.f, 0.f, 0.f, 0.f};
@@ -238,8 +298,14 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tm, __nv_bfloat16* __res
           uint32_t pk[16];
 #pragma unroll
           for (int i = 0; i < 32; i += 2) {
-            const float p0 = ex2_approx(fmaf(v[c + i], scale_log2, -moff));       // masked columns: exp2(-inf) = 0
-            const float p1 = ex2_approx(fmaf(v[c + i + 1], scale_log2, -moff));
+            float p0, p1;
+            if (ATTN_POLY_EVERY > 0 && ((i >> 1) % (ATTN_POLY_EVERY > 0 ? ATTN_POLY_EVERY : 1)) == ATTN_POLY_EVERY - 1) {
+              p0 = ex2_poly(fmaf(v[c + i], scale_log2, -moff));                   // masked columns: 2^-126
+              p1 = ex2_poly(fmaf(v[c + i + 1], scale_log2, -moff));
+            } else {
+              p0 = ex2_approx(fmaf(v[c + i], scale_log2, -moff));                 // masked columns: exp2(-inf) = 0
+              p1 = ex2_approx(fmaf(v[c + i + 1], scale_log2, -moff));
+            }
             ls4[(i >> 1) & 3] += p0 + p1;
             pk[i >> 1] = pack2(p0, p1);
           }
