@@ -319,6 +319,7 @@ class _FlowBase:
             self._programs[key] = p
         return p
 
+    @torch.inference_mode()
     def encode_batch(self, tokens: Sequence[torch.Tensor], n_prompt: Sequence[int], mel_lens: Sequence[Tuple[int, int]],
                      embeddings: Sequence[torch.Tensor], sample_rate: int = 22050) -> _Program:
         """tokens[b]: int [n_b] prompt + generated tokens of utterance b; mel_lens[b] = (mel_len1, mel_len2).

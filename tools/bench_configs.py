@@ -127,6 +127,64 @@ def run_stream(args):
     print(json.dumps(line))
 
 
+def run_stream_tokens(args):
+    """Config 3 through the reference-facing call: CosyVoice2Model.token2wav (cli/model.py:334-366) per chunk, i.e. the
+    whole flow.inference (token embedding, chunk-masked UpsampleConformerEncoder, causal CFM) + HiFT with its caches, from
+    speech tokens on the host to the chunk waveform on the host."""
+    from cosyvoice_b200.frontend import B200CausalMaskedDiffWithXvec
+    from cosyvoice_b200.hift import B200HiFTGenerator
+    from cosyvoice_b200.token2wav import Token2Wav2
+    dev = torch.device("cuda:0")
+    torch.cuda.set_device(dev)
+    dt = torch.bfloat16 if args.dtype == "bf16" else torch.float32
+    flow = B200CausalMaskedDiffWithXvec(synthetic.flow_frontend_sd(True, seed=2), dtype=dt, device=dev,
+                                        estimator_state_dict=synthetic.flow_estimator_sd(True, seed=0))
+    flow.decoder.use_cuda_graph = not args.eager
+    hift = B200HiFTGenerator(synthetic.hift_sd(True, seed=1), v2=True, dtype=dt, device=dev)
+    m = Token2Wav2(flow, hift, device=dev)
+    flow.encoder.static_chunk_size = 2 * flow.input_frame_rate          # cli/model.py:314
+    hop, prompt_tok, look = args.hop, 75, 3
+    tok, ptok, pfeat, emb = synthetic.frontend_inputs(True, args.chunks * hop + look, prompt_tok, seed=7)
+
+    def session(record):
+        m.open_session("s")
+        for k in range(args.chunks):
+            n = (k + 1) * hop + look
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            wav = m.token2wav(tok[:, :n], ptok, pfeat, emb, "s", k * hop, finalize=False)
+            wav_host = wav.cpu()
+            record(k, 2 * (prompt_tok + n), (time.perf_counter() - t0) * 1e3, wav_host.shape[-1])
+        m.close_session("s")
+
+    cold = {}
+    session(lambda k, T, ms, n: cold.__setitem__(k, ms))
+    session(lambda *a: None)
+    warm = {k: [] for k in range(args.chunks)}
+    meta = {}
+
+    def rec(k, T, ms, n):
+        warm[k].append(ms)
+        meta[k] = (T, n)
+    for _ in range(args.reps):
+        session(rec)
+    allv = [v for k in warm for v in warm[k]]
+    # front-end alone (device time) at the last chunk's length
+    n = args.chunks * hop + look
+    cat = torch.cat([ptok, tok[:, :n]], 1).reshape(-1)
+    prog = flow.encode_batch([cat], [prompt_tok], [(2 * prompt_tok, 2 * n)], [emb])
+    front = _timed(prog.run, 10)
+    print(json.dumps({
+        "config": 3, "workload": f"CosyVoice2Model.token2wav per chunk from speech tokens (front-end + causal CFM + HiFT + caches), "
+                                 f"hop {hop} tokens, prompt {prompt_tok} tokens, {args.chunks} chunks x {args.reps} sessions",
+        "dtype": args.dtype, "metric": "chunk_latency_ms", "p50": _pct(allv, 0.5), "p99": _pct(allv, 0.99), "max": max(allv),
+        "per_chunk": [{"k": k, "T": meta[k][0], "samples": meta[k][1], "p50_ms": _pct(warm[k], 0.5), "cold_ms": cold[k]}
+                      for k in range(args.chunks)],
+        "audio_ms_per_chunk": 1000.0 * 2 * hop * hift.hop / 24000.0,
+        "frontend_device_ms_last_chunk": _pct(front, 0.5), "frontend_launches": len(prog.ops) + 2,
+    }))
+
+
 # ----------------------------------------------------------------------------- config 4: BigVGAN
 def run_bigvgan(args):
     """BigVGAN trunk (BigVGAN/bigvgan.py:406-436) on `batch` synthetic mels N(0,1)*2-4 of the given frame counts,
@@ -275,6 +333,7 @@ def main():
     s.add_argument("--reps", type=int, default=5)
     s.add_argument("--dtype", default="bf16")
     s.add_argument("--eager", action="store_true")
+    s.add_argument("--from-tokens", action="store_true", help="measure through Token2Wav2.token2wav (front-end included)")
     b = sub.add_parser("bigvgan")
     b.add_argument("--batch", type=int, default=64)
     b.add_argument("--frames", default="94,938")
@@ -289,6 +348,9 @@ def main():
     w.add_argument("--eager", action="store_true")
     args = ap.parse_args()
     _lib.load()
+    if args.cmd == "stream" and args.from_tokens:
+        run_stream_tokens(args)
+        return
     {"stream": run_stream, "bigvgan": run_bigvgan, "sweep": run_sweep}[args.cmd](args)
 
 

@@ -14,11 +14,13 @@ ap = argparse.ArgumentParser()
 ap.add_argument("--batch", type=int, default=32)
 ap.add_argument("--timesteps", type=int, default=10)
 a = ap.parse_args()
+import bench  # noqa: E402  (utterance_inputs: the bench's synthetic tokens / prompt / noise)
+
 be = AcousticBackend(synthetic.flow_estimator_sd(False, seed=0), synthetic.hift_sd(False, seed=1), v2=False,
-                     dtype=torch.bfloat16, device="cuda")
+                     dtype=torch.bfloat16, device="cuda", frontend_sd=synthetic.flow_frontend_sd(False, seed=2))
 be.cfm.use_cuda_graph = False
-mus, spks, conds, zs = synthetic.flow_inputs(a.batch, 937, 281)
-res = be.prepare_resident(mus, spks, conds, zs, [281] * a.batch)
-be.step_resident(res, a.timesteps)
+toks, ptoks, pfeats, embs, zs = bench.utterance_inputs(a.batch)
+res = be.prepare_resident_tokens(toks, ptoks, pfeats, embs, zs, sample_rate=bench.SR)     # runs the front-end once (binding)
+be.step_resident(res, a.timesteps)                                                         # front-end + CFM + HiFT
 torch.cuda.synchronize()
 print("ok", float(res["hprog"].wav.abs().max()))
