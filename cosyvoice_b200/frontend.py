@@ -115,7 +115,7 @@ class _Weights:
             self.reg_out = linear_plan(sd[r + "12.weight"], sd[r + "12.bias"], dtype, device, c_pad=PAD80)
         self._pos: Dict[Tuple[int, int], List[torch.Tensor]] = {}
 
-    def pos_tables(self, half: int, engine_unused: int = 0) -> Tuple[List[torch.Tensor], List[torch.Tensor]]:
+    def pos_tables(self, half: int) -> Tuple[List[torch.Tensor], List[torch.Tensor]]:
         """P_l[center - r] = linear_pos_l(PE(r)) for |r| < half, one fp32 [2*half-1 (padded), 512] table per layer: input
         independent, so it is computed once per table size (on the device, fp32 CUDA-core GEMM) and shared by every
         sequence and call (the reference recomputes linear_pos(pos_emb) per layer per call, attention.py:292-294)."""
@@ -133,7 +133,7 @@ class _Weights:
                     ops.gemm_op(lw.pos32, A, lay, out, engine=_lib.ENGINE_SIMT, bias=False)()
                     g.append(out[:n_rel])
                 tabs.append(g)
-            if len(self._pos) >= 4:
+            if len(self._pos) >= 8:
                 self._pos.pop(next(iter(self._pos)))
             self._pos[key] = tabs
         t = self._pos[key]
@@ -303,17 +303,19 @@ class _FlowBase:
 
     # ---- batched front-end ---------------------------------------------------------------------------------------
     def _layouts(self, tok_lens: Sequence[int], mel_lens: Sequence[int]) -> Tuple[SeqLayout, SeqLayout]:
+        # one token stride per batch (that of its longest utterance): ragged batches of one length bucket share a program
+        stride = (max(int(l) for l in tok_lens) + 8 + 127) // 128 * 128
+        tok = SeqLayout(tok_lens, [stride] * len(tok_lens), self.device)
         if self.V2:
-            tok = SeqLayout.build(tok_lens, self.device, align=128, halo=8)
             return tok, tok.derive(2, 1, list(mel_lens))
-        return SeqLayout.build(tok_lens, self.device, align=128, halo=8), self.decoder.estimator.layout_for(mel_lens)
+        return tok, self.decoder.estimator.layout_for(mel_lens)
 
     def _program(self, tok: SeqLayout, mel: SeqLayout) -> _Program:
         chunk = int(self.encoder.static_chunk_size)
         key = (tok.stride_key(), mel.stride_key(), chunk)
         p = self._programs.get(key)
         if p is None:
-            if len(self._programs) >= 16:
+            if len(self._programs) >= 32:
                 self._programs.pop(next(iter(self._programs))).release()
             p = _Program(self.weights, tok, mel, self.engine, chunk)
             self._programs[key] = p

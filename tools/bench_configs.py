@@ -263,24 +263,36 @@ def run_sweep(args):
     SR, HOP, PROMPT = 24000, 256, 281
     g = torch.Generator().manual_seed(2048)
     dur = 2.0 + 28.0 * torch.rand(args.utterances, generator=g)
-    gen_frames = [int(round(float(d) * SR / HOP)) for d in dur]
+    n_tok = [int(round(25.0 * float(d))) for d in dur]                    # 25 speech tokens per second
+    gen_frames = [int(n / 25 * SR / 256) for n in n_tok] if not args.from_mu else [int(round(float(d) * SR / HOP)) for d in dur]
     tot = [PROMPT + f for f in gen_frames]
     costs = [shard.utterance_cost(t, f) for t, f in zip(tot, gen_frames)]
     mine = shard.lpt_assign(costs, world)[rank]
     batches = shard.make_batches(mine, tot, row_budget=args.row_budget, align=256, max_batch=args.max_batch)
     be = AcousticBackend(synthetic.flow_estimator_sd(False, seed=0), synthetic.hift_sd(False, seed=1), v2=False,
-                         dtype=torch.bfloat16, device=dev)
+                         dtype=torch.bfloat16, device=dev,
+                         frontend_sd=None if args.from_mu else synthetic.flow_frontend_sd(False, seed=2))
     be.cfm.use_cuda_graph = not args.eager
 
     def one_pass():
         n_samples = 0
         for b in batches:
-            mus, spks, conds, zs = [], [], [], []
-            for u in b:
-                m, s, c, z = synthetic.flow_inputs(1, gen_frames[u], PROMPT, first_index=u)
-                mus += m; spks += s; conds += c; zs += z
+            if args.from_mu:
+                mus, spks, conds, zs = [], [], [], []
+                for u in b:
+                    m, s, c, z = synthetic.flow_inputs(1, gen_frames[u], PROMPT, first_index=u)
+                    mus += m; spks += s; conds += c; zs += z
+            else:
+                toks, ptoks, pfeats, embs, zs = [], [], [], [], []
+                for u in b:
+                    t, pt, pf, e = synthetic.frontend_inputs(False, n_tok[u], 75, seed=1234 + u, sample_rate=SR)
+                    toks.append(t), ptoks.append(pt), pfeats.append(pf), embs.append(e)
+                    zs.append(torch.randn(1, 80, tot[u], generator=torch.Generator().manual_seed(4321 + u)))
             t_in = time.perf_counter()
-            wavs = be.synthesize_batch(mus, spks, conds, zs, [PROMPT] * len(b))
+            if args.from_mu:
+                wavs = be.synthesize_batch(mus, spks, conds, zs, [PROMPT] * len(b))
+            else:
+                wavs = be.synthesize_tokens_batch(toks, ptoks, pfeats, embs, zs, sample_rate=SR)
             host = [w.cpu() for w in wavs]
             one_pass.gpu_s += time.perf_counter() - t_in
             n_samples += sum(int(h.shape[-1]) for h in host)
@@ -312,7 +324,8 @@ def run_sweep(args):
     if rank == 0:
         audio_s = float(sm[1].item()) / SR
         print(json.dumps({
-            "config": 5, "workload": f"{args.utterances} utterances, gen 2-30 s + 3 s prompt, v1 flow + HiFT, "
+            "config": 5, "workload": f"{args.utterances} utterances, gen 2-30 s + 3 s prompt, v1 flow + HiFT "
+                                     f"{'from the encoder output' if args.from_mu else 'from speech tokens (flow.inference + hift.inference)'}, "
                                      f"utterance-sharded x{world}", "dtype": "bf16", "n_gpus": world,
             "metric": "audio_seconds_per_second", "value": audio_s / t, "seconds": t, "wall_with_input_synthesis": wall,
             "audio_seconds": audio_s, "batches_total": int(sm[3].item()), "cuda_graph": not args.eager,
@@ -346,6 +359,7 @@ def main():
     w.add_argument("--row-budget", type=int, default=48 * 1024)
     w.add_argument("--max-batch", type=int, default=64)
     w.add_argument("--eager", action="store_true")
+    w.add_argument("--from-mu", action="store_true", help="start at the encoder output (the pre-front-end measurement)")
     args = ap.parse_args()
     _lib.load()
     if args.cmd == "stream" and args.from_tokens:
