@@ -105,21 +105,36 @@ __global__ void __launch_bounds__(256) layernorm_seq_kernel(const float* __restr
 }
 
 // ---------------------------------------------------------------------------- relative-position self-attention
-// RelPositionMultiHeadedAttention (transformer/attention.py:243-330) for one (32-query tile, head, sequence) per CTA:
+// RelPositionMultiHeadedAttention (transformer/attention.py:243-330) for one (64-query tile, head, sequence) per CTA:
 //   s[i,j] = ((q_i + u_h) . k_j + (q_i + v_h) . P[i - j]) * scale,  P[r] = linear_pos(PE(r)) (rel_shift is the index i - j),
 //   key j visible iff j < len and (chunk == 0 or j < (i / chunk + 1) * chunk)   (utils/mask.py:116-124, all left chunks),
 //   out = softmax_j(s) V.
-// fp32 on the CUDA cores (parity mode and bf16 mode share it: the front-end is token-rate work).  Flash-style: 64-key
-// tiles, running max / sum per query row; K, V, the 95 rows of P a tile can touch and the score tile live in shared
-// memory, every shared load is a conflict-free 128-bit (scores) or 64-bit (PV) access.
-constexpr int RA_BQ = 32, RA_BK = 64, RA_D = 64, RA_LD = 68, RA_NP = RA_BQ + RA_BK - 1;
-constexpr int RA_SMEM_FLOATS = 2 * RA_BQ * RA_LD + RA_BK * RA_LD + RA_BK * RA_D + RA_NP * RA_LD + RA_BQ * RA_LD;
+// fp32 on the CUDA cores (parity mode and bf16 mode share it: the front-end is token-rate work).  Flash-style over 64-key
+// tiles with running max / sum per query row.  The first version (32-query tiles, one query x 8 keys per thread, tiles
+// loaded synchronously) ran at 12 TFLOP/s: ncu showed the tile fill (STS waiting on its LDG) and the LDS queue as the
+// stalls, FMA pipe 25 % (profiles/r01_ncu_relpos.md).  This version
+//   * gives every thread a 4 x 4 block of (query, key) pairs: the 16 pairs share 4 K rows, 8 Q rows and only 7 rows of P
+//     (those with equal i - j), 19 shared loads per 128 FMAs instead of 18 per 64;
+//   * stores K and P with an XOR swizzle of the 16-byte chunk index by (row / 4), so that the 16 threads that read rows
+//     4 apart hit 16 different chunks (conflict-free LDS.128);
+//   * double-buffers the K / V / P tiles with cp.async (zero-fill for keys past the sequence end): the next tile is in
+//     flight during the score, softmax and PV phases of the current one.
+constexpr int RA_BQ = 64, RA_BK = 64, RA_D = 64, RA_LD = 68, RA_NP = RA_BQ + RA_BK - 1;
+constexpr int RA_STAGE_FLOATS = RA_BK * RA_D * 2 + RA_NP * RA_D;          // K, V, P of one key tile
+constexpr int RA_SMEM_FLOATS = 2 * RA_BQ * RA_LD + 2 * RA_STAGE_FLOATS + RA_BQ * RA_LD;
 
 __device__ __forceinline__ float dot4(const float4 a, const float4 b, float acc) {
   acc = fmaf(a.x, b.x, acc); acc = fmaf(a.y, b.y, acc); acc = fmaf(a.z, b.z, acc); return fmaf(a.w, b.w, acc);
 }
+__device__ __forceinline__ void cp_async16(float* smem_dst, const float* gsrc, bool valid) {
+  const unsigned dst = (unsigned)__cvta_generic_to_shared(smem_dst);
+  const int bytes = valid ? 16 : 0;                 // src-size 0: the 16 bytes are zero-filled
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(gsrc), "r"(bytes) : "memory");
+}
+// row-major [rows][64] floats with the 16-byte chunk index XOR-swizzled by (row / 4)
+__device__ __forceinline__ int ra_swz(int row, int chunk) { return row * RA_D + ((chunk ^ ((row >> 2) & 15)) << 2); }
 
-__global__ void __launch_bounds__(256, 2) relpos_attention_kernel(const float* __restrict__ qkv, int ld,
+__global__ void __launch_bounds__(256, 1) relpos_attention_kernel(const float* __restrict__ qkv, int ld,
                                                                   const float* __restrict__ pos, int ldp, int center,
                                                                   int n_rel, const float* __restrict__ bias_u,
                                                                   const float* __restrict__ bias_v, void* __restrict__ out,
@@ -128,26 +143,48 @@ __global__ void __launch_bounds__(256, 2) relpos_attention_kernel(const float* _
   extern __shared__ __align__(16) float ra_smem[];
   float* Qu = ra_smem;
   float* Qv = Qu + RA_BQ * RA_LD;
-  float* Ks = Qv + RA_BQ * RA_LD;
-  float* Vs = Ks + RA_BK * RA_LD;
-  float* Ps = Vs + RA_BK * RA_D;
-  float* Ss = Ps + RA_NP * RA_LD;
+  float* stage0 = Qv + RA_BQ * RA_LD;
+  float* Ss = stage0 + 2 * RA_STAGE_FLOATS;
   pdl_sync();
   const int b = blockIdx.z, h = blockIdx.y, i0 = blockIdx.x * RA_BQ;
   const int len = __ldg(lay.seq_len + b);
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const size_t row0 = (size_t)__ldg(lay.seq_row0 + b);
   const int dm = heads * RA_D;
-  // rows of this query tile past the sequence's stride do not exist
   const int stride_rows = (b + 1 < lay.n_seq ? __ldg(lay.seq_row0 + b + 1) : lay.rows) - (int)row0;
   if (i0 >= stride_rows) return;
   const float* qbase = qkv + row0 * ld + h * RA_D;
+  const int i_last = min(i0 + RA_BQ - 1, len - 1);
+  const int kmax = i0 < len ? (chunk > 0 ? min((i_last / chunk + 1) * chunk, len) : len) : 0;
+  const int n_tiles = (kmax + RA_BK - 1) / RA_BK;
+
+  auto load_tile = [&](int t) {                    // cp.async of key tile t into stage t & 1
+    float* Ks = stage0 + (t & 1) * RA_STAGE_FLOATS;
+    float* Vs = Ks + RA_BK * RA_D;
+    float* Ps = Vs + RA_BK * RA_D;
+    const int j0 = t * RA_BK;
+    for (int e = tid; e < RA_BK * (RA_D / 4); e += 256) {
+      const int r = e >> 4, c = e & 15;
+      const bool ok = j0 + r < len;
+      const float* src = qbase + (size_t)(ok ? j0 + r : 0) * ld + c * 4;
+      cp_async16(Ks + ra_swz(r, c), src + dm, ok);
+      cp_async16(Vs + r * RA_D + c * 4, src + 2 * dm, ok);
+    }
+    const int rel0 = i0 - j0 - (RA_BK - 1);        // relative position of P row 0 of this tile
+    for (int e = tid; e < RA_NP * (RA_D / 4); e += 256) {
+      const int r = e >> 4, c = e & 15;
+      const int trow = min(max(center - (rel0 + r), 0), n_rel - 1);
+      cp_async16(Ps + ra_swz(r, c), pos + (size_t)trow * ldp + h * RA_D + c * 4, true);
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+  };
+  if (n_tiles > 0) load_tile(0);
   // ---- Q tile (+ biases, * scale)
   for (int e = tid; e < RA_BQ * (RA_D / 4); e += 256) {
     const int r = e >> 4, c = (e & 15) * 4;
-    float4 q = make_float4(0.f, 0.f, 0.f, 0.f), qu = q, qv = q;
+    float4 qu = make_float4(0.f, 0.f, 0.f, 0.f), qv = qu;
     if (i0 + r < len) {
-      q = *reinterpret_cast<const float4*>(qbase + (size_t)(i0 + r) * ld + c);
+      const float4 q = *reinterpret_cast<const float4*>(qbase + (size_t)(i0 + r) * ld + c);
       const float4 u = *reinterpret_cast<const float4*>(bias_u + h * RA_D + c);
       const float4 v = *reinterpret_cast<const float4*>(bias_v + h * RA_D + c);
       qu = make_float4((q.x + u.x) * scale, (q.y + u.y) * scale, (q.z + u.z) * scale, (q.w + u.w) * scale);
@@ -156,60 +193,71 @@ __global__ void __launch_bounds__(256, 2) relpos_attention_kernel(const float* _
     *reinterpret_cast<float4*>(Qu + r * RA_LD + c) = qu;
     *reinterpret_cast<float4*>(Qv + r * RA_LD + c) = qv;
   }
-  const int tq = tid >> 3, tk = tid & 7;
-  const int iq = i0 + tq;
-  const int lim_q = iq < len ? (chunk > 0 ? min((iq / chunk + 1) * chunk, len) : len) : 0;
-  const int i_last = min(i0 + RA_BQ - 1, len - 1);
-  const int kmax = i0 < len ? (chunk > 0 ? min((i_last / chunk + 1) * chunk, len) : len) : 0;
-  float m_run[4], l_run[4], o[4][2];
+  // score phase: thread (tq4, tk4) owns queries 4*tq4 .. +3 and keys 4*tk4 .. +3
+  const int tq4 = tid >> 4, tk4 = tid & 15;
+  int lim_q[4];
 #pragma unroll
-  for (int r = 0; r < 4; ++r) { m_run[r] = -INFINITY; l_run[r] = 0.f; o[r][0] = o[r][1] = 0.f; }
+  for (int a = 0; a < 4; ++a) {
+    const int iq = i0 + 4 * tq4 + a;
+    lim_q[a] = iq < len ? (chunk > 0 ? min((iq / chunk + 1) * chunk, len) : len) : 0;
+  }
+  // softmax / PV phase: warp w owns query rows 8w .. 8w+7, lane owns output dims 2*lane, 2*lane+1
+  float m_run[8], l_run[8], o[8][2];
+#pragma unroll
+  for (int r = 0; r < 8; ++r) { m_run[r] = -INFINITY; l_run[r] = 0.f; o[r][0] = o[r][1] = 0.f; }
 
-  for (int j0 = 0; j0 < kmax; j0 += RA_BK) {
-    __syncthreads();        // previous tile fully consumed (and the Q tile written, first time round)
-    for (int e = tid; e < RA_BK * (RA_D / 4); e += 256) {
-      const int r = e >> 4, c = (e & 15) * 4;
-      float4 k = make_float4(0.f, 0.f, 0.f, 0.f), v = k;
-      if (j0 + r < len) {
-        k = *reinterpret_cast<const float4*>(qbase + (size_t)(j0 + r) * ld + dm + c);
-        v = *reinterpret_cast<const float4*>(qbase + (size_t)(j0 + r) * ld + 2 * dm + c);
+  for (int t = 0; t < n_tiles; ++t) {
+    const int j0 = t * RA_BK;
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+    __syncthreads();                 // tile t has landed; everyone is done with tile t-1 (stage (t+1)&1 and Ss are free)
+    if (t + 1 < n_tiles) load_tile(t + 1);
+    const float* Ks = stage0 + (t & 1) * RA_STAGE_FLOATS;
+    const float* Vs = Ks + RA_BK * RA_D;
+    const float* Ps = Vs + RA_BK * RA_D;
+    float acc[4][4];
+#pragma unroll
+    for (int a = 0; a < 4; ++a)
+#pragma unroll
+      for (int c = 0; c < 4; ++c) acc[a][c] = 0.f;
+    const int pr0 = 4 * tq4 - 4 * tk4 + (RA_BK - 1) - 3;      // P row of (a = 0, c = 3); (a, c) uses row pr0 + a - c + 3
+#ifndef RA_UNROLL
+#define RA_UNROLL 2
+#endif
+    constexpr int kUnroll = RA_UNROLL;
+#pragma unroll kUnroll
+    for (int ch = 0; ch < RA_D / 4; ++ch) {
+      float4 qu[4], qv[4], kk[4], pp[7];
+#pragma unroll
+      for (int a = 0; a < 4; ++a) {
+        qu[a] = *reinterpret_cast<const float4*>(Qu + (4 * tq4 + a) * RA_LD + ch * 4);
+        qv[a] = *reinterpret_cast<const float4*>(Qv + (4 * tq4 + a) * RA_LD + ch * 4);
       }
-      *reinterpret_cast<float4*>(Ks + r * RA_LD + c) = k;
-      *reinterpret_cast<float4*>(Vs + r * RA_D + c) = v;
+#pragma unroll
+      for (int c = 0; c < 4; ++c) kk[c] = *reinterpret_cast<const float4*>(Ks + ra_swz(4 * tk4 + c, ch));
+#pragma unroll
+      for (int e = 0; e < 7; ++e) pp[e] = *reinterpret_cast<const float4*>(Ps + ra_swz(pr0 + e, ch));
+#pragma unroll
+      for (int a = 0; a < 4; ++a)
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+          acc[a][c] = dot4(qu[a], kk[c], acc[a][c]);
+          acc[a][c] = dot4(qv[a], pp[a - c + 3], acc[a][c]);
+        }
     }
-    const int rel0 = i0 - j0 - (RA_BK - 1);       // relative position of P row 0 of this tile
-    for (int e = tid; e < RA_NP * (RA_D / 4); e += 256) {
-      const int r = e >> 4, c = (e & 15) * 4;
-      const int trow = min(max(center - (rel0 + r), 0), n_rel - 1);
-      *reinterpret_cast<float4*>(Ps + r * RA_LD + c) =
-          *reinterpret_cast<const float4*>(pos + (size_t)trow * ldp + h * RA_D + c);
+#pragma unroll
+    for (int a = 0; a < 4; ++a) {
+      float4 sv;
+      sv.x = (j0 + 4 * tk4 + 0 < lim_q[a]) ? acc[a][0] : -INFINITY;
+      sv.y = (j0 + 4 * tk4 + 1 < lim_q[a]) ? acc[a][1] : -INFINITY;
+      sv.z = (j0 + 4 * tk4 + 2 < lim_q[a]) ? acc[a][2] : -INFINITY;
+      sv.w = (j0 + 4 * tk4 + 3 < lim_q[a]) ? acc[a][3] : -INFINITY;
+      *reinterpret_cast<float4*>(Ss + (4 * tq4 + a) * RA_LD + 4 * tk4) = sv;
     }
     __syncthreads();
-    // ---- scores: thread (tq, tk) owns keys tk + 8c
-    float acc[8];
+    // ---- online softmax
 #pragma unroll
-    for (int c = 0; c < 8; ++c) acc[c] = 0.f;
-#pragma unroll 4
-    for (int d = 0; d < RA_D; d += 4) {
-      const float4 qu = *reinterpret_cast<const float4*>(Qu + tq * RA_LD + d);
-      const float4 qv = *reinterpret_cast<const float4*>(Qv + tq * RA_LD + d);
-#pragma unroll
-      for (int c = 0; c < 8; ++c) {
-        const int kk = tk + 8 * c;
-        acc[c] = dot4(qu, *reinterpret_cast<const float4*>(Ks + kk * RA_LD + d), acc[c]);
-        acc[c] = dot4(qv, *reinterpret_cast<const float4*>(Ps + (tq - kk + RA_BK - 1) * RA_LD + d), acc[c]);
-      }
-    }
-#pragma unroll
-    for (int c = 0; c < 8; ++c) {
-      const int kk = tk + 8 * c;
-      Ss[tq * RA_LD + kk] = (j0 + kk < lim_q) ? acc[c] : -INFINITY;
-    }
-    __syncthreads();
-    // ---- online softmax + PV: warp w owns query rows 4w .. 4w+3, lane owns output dims 2*lane, 2*lane+1
-#pragma unroll
-    for (int r = 0; r < 4; ++r) {
-      const int rr = warp * 4 + r;
+    for (int r = 0; r < 8; ++r) {
+      const int rr = warp * 8 + r;
       const float s0 = Ss[rr * RA_LD + lane], s1 = Ss[rr * RA_LD + lane + 32];
       float mx = fmaxf(s0, s1);
 #pragma unroll
@@ -229,14 +277,15 @@ __global__ void __launch_bounds__(256, 2) relpos_attention_kernel(const float* _
       o[r][1] *= alpha;
     }
     __syncwarp();
-#pragma unroll 4
+    // ---- O += P V
+#pragma unroll 2
     for (int j = 0; j < RA_BK; j += 4) {
       float2 v[4];
 #pragma unroll
       for (int jj = 0; jj < 4; ++jj) v[jj] = *reinterpret_cast<const float2*>(Vs + (j + jj) * RA_D + 2 * lane);
 #pragma unroll
-      for (int r = 0; r < 4; ++r) {
-        const float4 p = *reinterpret_cast<const float4*>(Ss + (warp * 4 + r) * RA_LD + j);
+      for (int r = 0; r < 8; ++r) {
+        const float4 p = *reinterpret_cast<const float4*>(Ss + (warp * 8 + r) * RA_LD + j);
         o[r][0] = fmaf(p.x, v[0].x, o[r][0]); o[r][1] = fmaf(p.x, v[0].y, o[r][1]);
         o[r][0] = fmaf(p.y, v[1].x, o[r][0]); o[r][1] = fmaf(p.y, v[1].y, o[r][1]);
         o[r][0] = fmaf(p.z, v[2].x, o[r][0]); o[r][1] = fmaf(p.z, v[2].y, o[r][1]);
@@ -246,8 +295,8 @@ __global__ void __launch_bounds__(256, 2) relpos_attention_kernel(const float* _
   }
   // ---- write (zeros on rows past the valid length)
 #pragma unroll
-  for (int r = 0; r < 4; ++r) {
-    const int i = i0 + warp * 4 + r;
+  for (int r = 0; r < 8; ++r) {
+    const int i = i0 + warp * 8 + r;
     if (i >= stride_rows) continue;
     float a = 0.f, c = 0.f;
     if (i < len && l_run[r] > 0.f) { a = o[r][0] / l_run[r]; c = o[r][1] / l_run[r]; }
