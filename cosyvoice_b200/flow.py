@@ -310,6 +310,7 @@ class B200Estimator:
         self.weights = _Weights(state_dict, causal, dtype, self.device)
         self.static_chunk_size = 0          # attribute written by cli/model.py:50,315
         self._programs: Dict[tuple, _Program] = {}
+        self.serial = ops.Serial()          # programs and solver state are shared scratch: one user at a time
 
     def layout_for(self, lens: Sequence[int]) -> SeqLayout:
         align = 128 * (2 ** (len(self.weights.down) - 1))
@@ -334,6 +335,11 @@ class B200Estimator:
         """x, mu, cond [N,80,T]; mask [N,1,T]; t [N]; spks [N,80] -> [N,80,T] (flow/decoder.py:222-334)."""
         N, _, T = x.shape
         lens = [int(v) for v in mask.reshape(N, T).sum(dim=1).round().tolist()]
+        with self.serial:
+            return self._forward_locked(x, mu, t, spks, cond, lens, taps)
+
+    def _forward_locked(self, x, mu, t, spks, cond, lens, taps):
+        N, _, T = x.shape
         lay = self.layout_for(lens)
         prog = self.program(lay)
         f32 = lambda a: a.detach().to(self.device, torch.float32)
@@ -459,6 +465,10 @@ class B200ConditionalCFM:
                     zs: Sequence[torch.Tensor], n_timesteps: int = 10) -> List[torch.Tensor]:
         """mus/conds/zs: per-utterance [1,80,T_u] (or [80,T_u]) fp32; spks [1,80].  Returns per-utterance
         mel [1,80,T_u] fp32."""
+        with self.estimator.serial:
+            return self._solve_batch_locked(mus, spks, conds, zs, n_timesteps)
+
+    def _solve_batch_locked(self, mus, spks, conds, zs, n_timesteps):
         B = len(mus)
         lens = [int(m.shape[-1]) for m in mus]
         lay1 = self.estimator.layout_for(lens)

@@ -290,6 +290,7 @@ class _FlowBase:
         self.decoder = (B200CausalConditionalCFM if self.V2 else B200ConditionalCFM)(est)
         self.encoder = _EncoderHandle()
         self._programs: Dict[tuple, _Program] = {}
+        self.serial = ops.Serial()              # front-end programs are shared scratch: one user (thread / stream) at a time
 
     # the reference calls these on the module (cli/model.py:43-45,76-81)
     def half(self):
@@ -357,6 +358,10 @@ class _FlowBase:
         """Throughput entry: B utterances through front-end + CFM in one varlen batch; per-utterance results equal the
         B = 1 `inference` calls with the same noise (zs[b] [1,80,T_b]; drawn with torch.randn on the device when None).
         Returns the generated mels [1, 80, mel_len2_b] fp32 (device)."""
+        with self.serial, self.decoder.estimator.serial:
+            return self._inference_batch_locked(tokens, prompt_tokens, prompt_feats, embeddings, zs, n_timesteps, sample_rate)
+
+    def _inference_batch_locked(self, tokens, prompt_tokens, prompt_feats, embeddings, zs, n_timesteps, sample_rate):
         B = len(tokens)
         n_prompt = [int(p.numel()) for p in prompt_tokens]
         mel_lens = [self._mel_lens(n_prompt[b], int(tokens[b].numel()), int(prompt_feats[b].shape[-2]), sample_rate)
@@ -414,15 +419,16 @@ class B200MaskedDiffWithXvec(_FlowBase):
             raise ValueError("padded token tensors are not supported: token_len must equal token.shape[1] (B = 1)")
         mel_len1, mel_len2 = self._mel_lens(n1, n2, int(prompt_feat.shape[1]), sample_rate)
         tok = torch.cat([prompt_token.reshape(-1), token.reshape(-1)]).to(torch.int32)
-        prog = self.encode_batch([tok], [n1], [(mel_len1, mel_len2)], [embedding], sample_rate)
         T = mel_len1 + mel_len2
-        mu = self._mu_nct(prog, T)
+        with self.serial:
+            prog = self.encode_batch([tok], [n1], [(mel_len1, mel_len2)], [embedding], sample_rate)
+            mu, spk = self._mu_nct(prog, T), prog.spks[0:1].clone()
         conds = torch.zeros(1, T, N_FEATS, dtype=torch.float32, device=self.device)          # flow.py:144-146
         conds[:, :mel_len1] = prompt_feat.to(self.device, torch.float32)
         mask = torch.ones(1, 1, T, dtype=torch.float32, device=self.device)
         if flow_cache is not None:
             flow_cache = flow_cache.to(self.device, torch.float32)
-        feat, flow_cache = self.decoder(mu=mu, mask=mask, spks=prog.spks[0:1].clone(), cond=conds.transpose(1, 2).contiguous(),
+        feat, flow_cache = self.decoder(mu=mu, mask=mask, spks=spk, cond=conds.transpose(1, 2).contiguous(),
                                         n_timesteps=n_timesteps, prompt_len=mel_len1, flow_cache=flow_cache)
         feat = feat[:, :, mel_len1:]
         assert feat.shape[2] == mel_len2
@@ -460,13 +466,14 @@ class B200CausalMaskedDiffWithXvec(_FlowBase):
             raise ValueError("padded token tensors are not supported: token_len must equal token.shape[1] (B = 1)")
         mel_len1, mel_len2 = self._mel_lens(n1, n2, int(prompt_feat.shape[1]), sample_rate)
         tok = torch.cat([prompt_token.reshape(-1), token.reshape(-1)]).to(torch.int32)
-        prog = self.encode_batch([tok], [n1], [(mel_len1, mel_len2)], [embedding], sample_rate)
         T = mel_len1 + mel_len2
-        mu = self._mu_nct(prog, T)
+        with self.serial:
+            prog = self.encode_batch([tok], [n1], [(mel_len1, mel_len2)], [embedding], sample_rate)
+            mu, spk = self._mu_nct(prog, T), prog.spks[0:1].clone()
         conds = torch.zeros(1, T, N_FEATS, dtype=torch.float32, device=self.device)          # flow.py:301-303
         conds[:, :mel_len1] = prompt_feat.to(self.device, torch.float32)
         mask = torch.ones(1, 1, T, dtype=torch.float32, device=self.device)
-        feat, _ = self.decoder(mu=mu, mask=mask, spks=prog.spks[0:1].clone(), cond=conds.transpose(1, 2).contiguous(),
+        feat, _ = self.decoder(mu=mu, mask=mask, spks=spk, cond=conds.transpose(1, 2).contiguous(),
                                n_timesteps=n_timesteps)
         feat = feat[:, :, mel_len1:]
         assert feat.shape[2] == mel_len2

@@ -294,6 +294,7 @@ class B200HiFTGenerator:
         self.sampling_rate = sampling_rate
         self.hop = self.weights.hop
         self._programs: Dict[tuple, _Program] = {}
+        self.serial = ops.Serial()          # cached programs are shared scratch: one user (thread / stream) at a time
 
     def program(self, lens: Sequence[int], uniform_stride: bool = False) -> _Program:
         """Programs are cached per stride pattern (128-frame buckets) and re-bound to the lengths of each call.
@@ -330,6 +331,10 @@ class B200HiFTGenerator:
                         ) -> Tuple[List[torch.Tensor], List[torch.Tensor]]:
         """mels: per-utterance [1,80,T_u].  phase_vec [B,9,1] / noise [B,9,L_max]: injected RNG (tests);
         source [B,1,L_max]: bypass the source module entirely.  Returns ([wav [1,L_u]], [s [1,1,L_u]])."""
+        with self.serial:
+            return self._inference_batch_locked(mels, phase_vec, noise, cache_sources, source, uniform_stride)
+
+    def _inference_batch_locked(self, mels, phase_vec, noise, cache_sources, source, uniform_stride):
         lens = [int(m.shape[-1]) for m in mels]
         prog = self.program(lens, uniform_stride)
         B, dev = len(lens), self.device

@@ -6,6 +6,7 @@ pre-marshalled, so that a model forward is a flat list of launches (cheap to rep
 capture in a CUDA graph).
 """
 import ctypes as C
+import threading
 from typing import Callable, Optional
 
 import torch
@@ -16,6 +17,39 @@ from .layout import SeqLayout
 from .packing import TapPlan
 
 Op = Callable[[], None]
+
+
+import os as _os
+_NO_SERIAL = _os.environ.get("CVB200_NO_SERIAL", "0") == "1"
+
+
+class Serial:
+    """Serialises the use of an object's cached programs (pre-sized buffers + pre-marshalled launches) across host threads
+    AND CUDA streams.  The reference allocates per call, so several `tts()` sessions and the LLM thread's stream may be
+    inside flow / hift at once (cosyvoice/cli/model.py:62-69,119,183-189; SURVEY.md 8b "Threading"); here a call holds the
+    lock while it binds inputs and enqueues its launches, waits (on the device, not the host) for the previous user's
+    last launch if that ran on another stream, and leaves an event behind.  Nothing synchronises the device."""
+
+    def __init__(self):
+        self._lock = threading.RLock()
+        self._event: Optional[torch.cuda.Event] = None
+
+    def __enter__(self):
+        if _NO_SERIAL:                  # CVB200_NO_SERIAL=1: A/B switch that shows tests/test_gpu_concurrency.py failing
+            return self
+        self._lock.acquire()
+        if self._event is not None:
+            torch.cuda.current_stream().wait_event(self._event)
+        return self
+
+    def __exit__(self, *exc):
+        if _NO_SERIAL:
+            return False
+        ev = torch.cuda.Event()
+        ev.record()
+        self._event = ev
+        self._lock.release()
+        return False
 
 # bench.py's roofline leg: when a list is installed here, every GEMM / attention launch is bracketed by CUDA
 # events on the launching stream and (kind, algorithmic_flops, start, end) is appended to it.

@@ -107,6 +107,10 @@ class AcousticBackend:
     @torch.inference_mode()
     def step_resident(self, r: dict, n_timesteps: int = 10):
         """One pass over the batch with every input already in HBM (noise, mu, cond, spks)."""
+        with self.cfm.estimator.serial, self.hift.serial:
+            return self._step_resident_locked(r, n_timesteps)
+
+    def _step_resident_locked(self, r: dict, n_timesteps: int):
         st, lay1, hprog = r["st"], r["lay1"], r["hprog"]
         if r.get("fprog") is not None:          # front-end inside the step: tokens -> mu, spks (flow/flow.py:126-141)
             r["fprog"].run()
