@@ -29,3 +29,15 @@ def pytest_collection_modifyitems(config, items):
 @pytest.fixture(scope="session")
 def golden_dir():
     return os.path.join(ROOT, "tests", "golden")
+
+
+@pytest.fixture(scope="session", autouse=True)
+def _flush_denormals():
+    """The oracle's CFG branch with all-zero conditioning produces denormals on the CPU (2.4x to 30x
+    slower torch kernels); flushing them changes results far below every tolerance stated in the tests."""
+    try:
+        import torch
+        torch.set_flush_denormal(True)
+    except Exception:
+        pass
+    yield
