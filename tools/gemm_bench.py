@@ -16,7 +16,13 @@ DEV = "cuda"
 bf = torch.bfloat16
 
 
+BN_OVERRIDE = 0
+
+
 def bench(name, plan, A, lay, out0, reps=10, **kw):
+    if BN_OVERRIDE and plan.n_pad % BN_OVERRIDE == 0:
+        plan.bn = BN_OVERRIDE      # experiment: N-tile width (tail balance / resident-W mode)
+        name = f"{name} [bn {BN_OVERRIDE}]"
     op = ops.gemm_op(plan, A, lay, out0, engine=_lib.ENGINE_TCGEN05, **kw)
     flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=DEV)
     for _ in range(3):
@@ -42,7 +48,10 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--rows", type=int, default=64 * 1280)
     ap.add_argument("--only", default="")
+    ap.add_argument("--bn", type=int, default=0, help="override the plan's N tile (0 = packing._choose_bn)")
     a = ap.parse_args()
+    global BN_OVERRIDE
+    BN_OVERRIDE = a.bn
     nseq = 64
     T = a.rows // nseq - 62
     lay = SeqLayout.build([T] * nseq, DEV, align=256)
