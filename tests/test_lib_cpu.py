@@ -50,3 +50,22 @@ def test_struct_sizes_match_c_layout():
     assert C.sizeof(_lib.Epilogue) == 8 * 8 + 16 * 4
     assert C.sizeof(_lib.Layout) == 4 * 8 + 3 * 4 + 4
     assert C.sizeof(_lib.Gemm) == 6 * 8 + 11 * 4 + 2 * 2 * 32 + 4 + C.sizeof(_lib.Epilogue)
+
+
+def test_product_package_never_reaches_the_oracle():
+    """oracle/ is test infrastructure: nothing under cosyvoice_b200/ may import or execute it (static scan of every
+    module of the package), and a missing shared library is a loud error, not a fallback."""
+    import subprocess
+    import sys
+    pkg = os.path.join(ROOT, "cosyvoice_b200")
+    for dirpath, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".h")):
+                src = open(os.path.join(dirpath, f)).read()
+                assert not re.search(r"^\s*(from|import)\s+oracle\b", src, flags=re.M), os.path.join(dirpath, f)
+                assert not re.search(r"import_module\(\s*['\"]oracle|__import__\(\s*['\"]oracle", src), os.path.join(dirpath, f)
+    code = ("import os, sys; os.environ['CVB200_LIB'] = '/nonexistent/libcvb200.so'; sys.path.insert(0, %r)\n"
+            "from cosyvoice_b200 import _lib\n"
+            "try:\n    _lib.load()\nexcept RuntimeError as e:\n    print('LOUD', e)\n" % ROOT)
+    out = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=120)
+    assert "LOUD" in out.stdout and "not found" in out.stdout, out.stdout + out.stderr
