@@ -281,6 +281,17 @@ int launch_tapgemm_tc(const GemmParams& p_in, cudaStream_t stream) {
   // Latency mode (streaming chunks: a handful of 128-row tiles): narrower N tiles put the problem on more SMs.
   // Each CTA then streams a quarter of the weights; the A tile is re-read from L2 by its N-tile siblings.
   while (p.bn % 128 == 0 && 2LL * p.m_tiles * p.n_phase * (p.n_pad / p.bn) <= sms) p.bn /= 2;
+  // A 256-wide tile whose weights do not fit the B region but whose two 128-wide halves do (K = 512: the attention
+  // out-projection) runs as two resident-W keys: W is fetched once per CTA instead of once per tile and the tail
+  // is 9 of 8.65 rounds instead of 5 of 4.3 (profiles/r01_gemm_bench.txt: 66.4 -> 62.6 us; K = 768 / 1024 / 1536
+  // stay non-resident at 128 and measured slower there).
+  {
+    const uint64_t Kfull = (uint64_t)p.n_seg * p.seg_len;
+    const uint64_t cap = (uint64_t)STAGES * B_STAGE_BYTES;
+    if (p.bn == 256 && (uint64_t)p.bn * Kfull * 2 > cap && 128ull * Kfull * 2 <= cap &&
+        p.m_tiles * p.n_phase * (p.n_pad / p.bn) > sms)
+      p.bn = 128;
+  }
   static std::once_flag attr_once;
   static cudaError_t attr_err = cudaSuccess;
   std::call_once(attr_once, [] {
