@@ -16,7 +16,7 @@ import torch
 pytestmark = pytest.mark.gpu
 
 from cosyvoice_b200 import ops
-from cosyvoice_b200.frontend import B200MaskedDiffWithXvec
+from cosyvoice_b200.frontend import B200CausalMaskedDiffWithXvec, B200MaskedDiffWithXvec
 from cosyvoice_b200.hift import B200HiFTGenerator
 from cosyvoice_b200.layout import SeqLayout
 from oracle import encoder_ref, flow_ref, hift_ref, init_weights
@@ -68,6 +68,35 @@ def test_config1_one_full_utterance_fp32_matches_the_oracle():
     werr = (wav - want_w).abs().max().item()
     print(f"full-size hift fp32: max-abs {werr:.3e}")
     assert wav.shape == (1, T2 * 256) and werr < 1e-3, werr
+
+
+def test_config3_size_one_full_v2_utterance_fp32_matches_the_oracle():
+    """CosyVoice2 at the size of BASELINE's streaming config once finalised (75 prompt + 250 tokens -> T = 150 + 500, L = 240 000):
+    CausalMaskedDiffWithXvec.inference (UpsampleConformer front-end + causal 10-step CFM) and the v2 HiFT decode against the oracle."""
+    tok, ptok, pfeat, emb = init_weights.frontend_inputs(True, N_TOK, N_PROMPT, seed=1234, sample_rate=SR)
+    fsd, esd = init_weights.flow_frontend_sd(True, seed=2), init_weights.flow_estimator_sd(True, seed=0)
+    torch.set_flush_denormal(True)
+    mu, spks, cond, l1, l2 = encoder_ref.frontend_v2(fsd, tok, ptok, pfeat, emb, static_chunk_size=0)
+    assert (l1, l2) == (150, 500)
+    z = torch.randn(1, 80, l1 + l2, generator=torch.Generator().manual_seed(4321))
+    want = flow_ref.solve_euler(esd, z, flow_ref.cosine_t_span(10), mu, torch.ones(1, 1, l1 + l2), spks, cond, causal=True)[:, :, l1:]
+    flow = B200CausalMaskedDiffWithXvec(fsd, dtype=torch.float32, device=DEV, estimator_state_dict=esd)
+    flow.decoder._noise = lambda m, _z=z: _z.to(m.device)
+    i32 = lambda n: torch.tensor([n], dtype=torch.int32)
+    got, _ = flow.inference(token=tok.to(DEV), token_len=i32(tok.shape[1]), prompt_token=ptok.to(DEV),
+                            prompt_token_len=i32(ptok.shape[1]), prompt_feat=pfeat.to(DEV), prompt_feat_len=i32(pfeat.shape[1]),
+                            embedding=emb.to(DEV), n_timesteps=10, finalize=True)
+    err = (got.cpu() - want).abs().max().item()
+    print(f"full-size v2 flow fp32: max-abs {err:.3e}")
+    assert got.shape == (1, 80, 500) and err < 2e-3, err
+    hsd = init_weights.hift_sd(True, seed=1)
+    src = torch.randn(1, 1, 500 * 480, generator=torch.Generator().manual_seed(8)) * 0.1
+    want_w = hift_ref.decode(hsd, want, src, v2=True)
+    hift = B200HiFTGenerator(hsd, v2=True, dtype=torch.float32, device=DEV)
+    wav = hift.inference_batch([want], source=src)[0][0].cpu()
+    werr = (wav - want_w).abs().max().item()
+    print(f"full-size v2 hift fp32: max-abs {werr:.3e}")
+    assert wav.shape == (1, 500 * 480) and werr < 1e-3, werr
 
 
 def test_config2_batch_members_are_independent_and_bf16_is_within_the_gap():
