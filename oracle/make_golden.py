@@ -248,6 +248,31 @@ def frontend(v2: bool):
     _save(f"frontend_{'v2' if v2 else 'v1'}.pt", dict(weights_seed=2, estimator_seed=0, v2=v2, cases=cases))
 
 
+def fullsize():
+    """BASELINE-size utterances (75 prompt + 250 tokens, 24 kHz) through the REAL flow.inference of both model versions:
+    v1 T = 281 + 937 (noise: torch.randn under manual_seed(4321), what randn_like draws), v2 T = 150 + 500 (rand_noise).
+    Inputs are regenerated from their seeds by the tests; only the generated mels are stored."""
+    out = {}
+    for v2 in (False, True):
+        est = R.build_estimator(v2).eval()
+        est.load_state_dict(W.flow_estimator_sd(v2, seed=0), strict=True)
+        m = R.build_flow(v2, est).eval()
+        m.load_state_dict(W.flow_frontend_sd(v2, seed=2), strict=False)
+        token, prompt_token, prompt_feat, embedding = W.frontend_inputs(v2, 250, 75, seed=1234, sample_rate=24000)
+        kw = dict(token=token, token_len=torch.tensor([250], dtype=torch.int32), prompt_token=prompt_token,
+                  prompt_token_len=torch.tensor([75], dtype=torch.int32), prompt_feat=prompt_feat,
+                  prompt_feat_len=torch.tensor([prompt_feat.shape[1]], dtype=torch.int32), embedding=embedding)
+        with torch.no_grad():
+            torch.manual_seed(4321)
+            if v2:
+                m.encoder.static_chunk_size = 0
+                mel, _ = m.inference(**kw, n_timesteps=10)
+            else:
+                mel, _ = m.inference(**kw, flow_cache=torch.zeros(1, 80, 0, 2), sample_rate=24000, n_timesteps=10)
+        out["v2" if v2 else "v1"] = dict(mel=mel.float().contiguous(), input_seed=1234, noise_seed=None if v2 else 4321)
+    _save("fullsize.pt", out)
+
+
 if __name__ == "__main__":
     import warnings
     warnings.filterwarnings("ignore")
@@ -263,3 +288,4 @@ if __name__ == "__main__":
     token2wav()
     frontend(False)
     frontend(True)
+    fullsize()

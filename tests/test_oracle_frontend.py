@@ -69,3 +69,18 @@ def test_regulator_segments_cover_the_output_once():
             assert ds == pos and s == src
             pos, src = pos + dn, src + n
         assert pos == l1 + l2 and src == n1 + n2
+
+
+def test_oracle_at_full_size_matches_the_reference_recording(golden_dir):
+    """BASELINE config 1 (v1, 75 prompt + 250 tokens -> T = 281 + 937): the oracle's whole flow.inference against the mel
+    the REAL MaskedDiffWithXvec.inference produced (oracle/make_golden.py fullsize()).  The v2 recording of the same
+    file is checked against the CUDA path (and the oracle) in tests/test_gpu_fullsize.py; on CPU it is a minute more."""
+    d = _load(golden_dir, "fullsize.pt")["v1"]
+    fsd, esd = init_weights.flow_frontend_sd(False, seed=2), init_weights.flow_estimator_sd(False, seed=0)
+    tok, ptok, pfeat, emb = init_weights.frontend_inputs(False, 250, 75, seed=d["input_seed"], sample_rate=24000)
+    mu, spks, cond, l1, l2 = E.frontend_v1(fsd, tok, ptok, pfeat, emb, sample_rate=24000)
+    assert (l1, l2) == (281, 937)
+    z = torch.randn(1, 80, l1 + l2, generator=torch.Generator().manual_seed(d["noise_seed"]))
+    mel = flow_ref.solve_euler(esd, z, flow_ref.cosine_t_span(10), mu, torch.ones(1, 1, l1 + l2), spks, cond)[:, :, l1:]
+    err = (mel - d["mel"]).abs().max().item()
+    assert mel.shape == d["mel"].shape and err < 1e-4, err
