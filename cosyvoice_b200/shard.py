@@ -3,7 +3,8 @@ partitioned by utterance with NO collective on the data path; NCCL/gloo is used 
 
   cost model   : algorithmic FLOPs of one utterance (SURVEY.md 8d formulas)
   lpt_assign   : longest-processing-time-first greedy assignment to ranks
-  make_batches : per-rank length-bucketed batches under a row budget (rows = varlen-packed frames)
+  make_batches : length-bucketed batches under a row budget (rows = varlen-packed frames)
+  assign_batches : batches formed over the WHOLE job, then LPT over batch costs (each rank keeps full batches)
   gather_by_index : optional result gather (all_gather of per-utterance tensors, padded)
 """
 import math
@@ -27,6 +28,14 @@ def hift_flops(T_gen: int, v2: bool = False) -> float:
 
 def utterance_cost(total_frames: int, gen_frames: int, v2: bool = False) -> float:
     return flow_flops(total_frames, v2) + hift_flops(gen_frames, v2)
+
+
+def batch_seconds(total_frames: Sequence[int], gen_frames: Sequence[int], v2: bool = False) -> float:
+    """Predicted B200 time of one varlen batch through flow.inference + hift.inference (bf16): least-squares fit to the
+    84 batches of config 5 on one GPU (profiles/r01_config5_batches_x1.json, rms error 4.5 %):
+    1.39 ms per algorithmic TFLOP + 3.25 us per frame + 21 ms per batch.  The weight assign_batches balances."""
+    flops = sum(utterance_cost(t, g, v2) for t, g in zip(total_frames, gen_frames))
+    return 1.39e-15 * flops + 3.25e-6 * sum(total_frames) + 0.021
 
 
 def lpt_assign(costs: Sequence[float], n_ranks: int) -> List[List[int]]:
@@ -57,6 +66,28 @@ def make_batches(indices: Sequence[int], lens: Sequence[int], row_budget: int = 
         idx = buckets[stride]
         batches += [idx[k:k + nb] for k in range(0, len(idx), nb)]
     return batches
+
+
+def assign_batches(costs: Sequence[float], lens: Sequence[int], n_ranks: int, row_budget: int = 48 * 1024,
+                   align: int = 256, max_batch: int = 64, max_imbalance: float = 1.05) -> List[List[List[int]]]:
+    """Per-rank batch lists.  Sharding single utterances (lpt_assign) and batching per rank leaves every rank a thin
+    slice of every stride bucket, i.e. more and smaller batches as the job spreads (config 5 on 8 GPUs: 136 batches
+    against 84 on one GPU).  Here the batches are formed over the whole job first and LPT runs
+    over the batch costs, so a rank's batches are as full as on one GPU.  Falls back to utterance-level sharding when
+    there are too few batches to balance (predicted max load / mean load > max_imbalance).  Deterministic: every rank
+    computes the same assignment from the same lengths, no communication.  Measured on 8 GPUs the two schemes tie
+    (6946 vs 7097 audio-s/s, profiles/r01_config5_sweep2048_x8*.jsonl): the 8 % below 8 x one GPU is each GPU's batches
+    running slower with 8 ranks on the box (host side of the ragged path), not the sharding."""
+    idx = list(range(len(costs)))
+    if n_ranks == 1:
+        return [make_batches(idx, lens, row_budget, align, max_batch)]
+    batches = make_batches(idx, lens, row_budget, align, max_batch)
+    bcost = [1.39e-15 * sum(costs[u] for u in b) + 3.25e-6 * sum(lens[u] for u in b) + 0.021 for b in batches]   # batch_seconds
+    asg = lpt_assign(bcost, n_ranks)
+    loads = [sum(bcost[i] for i in a) for a in asg]
+    if sum(loads) > 0 and max(loads) * n_ranks / sum(loads) <= max_imbalance:
+        return [[batches[i] for i in sorted(a)] for a in asg]
+    return [make_batches(mine, lens, row_budget, align, max_batch) for mine in lpt_assign(costs, n_ranks)]
 
 
 def gather_by_index(local: Dict[int, torch.Tensor], n_total: int, group=None) -> List[torch.Tensor]:

@@ -65,3 +65,32 @@ def test_batches_are_single_stride_bucket_and_patterns_repeat():
         assert len(strides) == 1
         patterns.add((strides.pop(), len(b)))
     assert len(patterns) <= 2 * 12            # <= one full + one partial pattern per 256-row bucket
+
+
+def test_batch_level_assignment_keeps_full_batches_and_falls_back():
+    """assign_batches: whole-job batches spread by LPT over batch costs -- every utterance exactly once, the same number
+    of batches as on one GPU (utterance-level sharding needs ~60 % more on 8 ranks), load within 5 %; with too few
+    batches to balance it returns the utterance-level sharding instead."""
+    g = torch.Generator().manual_seed(2048)
+    dur = 2 + 28 * torch.rand(2048, generator=g)
+    gen = [int(round(d.item() * 25) / 25 * 24000 / 256) for d in dur]
+    tot = [281 + t for t in gen]
+    costs = [shard.utterance_cost(t, f) for t, f in zip(tot, gen)]
+    one = shard.assign_batches(costs, tot, 1)[0]
+    for n in (2, 4, 8):
+        per_rank = shard.assign_batches(costs, tot, n)
+        assert sorted(u for r in per_rank for b in r for u in b) == list(range(2048))
+        assert sum(len(r) for r in per_rank) == len(one)
+        loads = [sum(costs[u] for b in r for u in b) for r in per_rank]
+        assert max(loads) / (sum(loads) / n) < 1.05
+        old = sum(len(shard.make_batches(m, tot)) for m in shard.lpt_assign(costs, n))
+        assert old > len(one)
+        for r in per_rank:
+            for b in r:
+                assert len({(tot[u] + 8 + 255) // 256 * 256 for u in b}) == 1
+    # 3 batches cannot be balanced over 2 ranks: utterance-level fallback (each rank batches its own share)
+    few_tot, few_cost = [1000] * 96 + [4000] * 8, [1.0] * 96 + [16.0] * 8
+    per_rank = shard.assign_batches(few_cost, few_tot, 2, row_budget=48 * 1024)
+    assert sorted(u for r in per_rank for b in r for u in b) == list(range(104))
+    loads = [sum(few_cost[u] for b in r for u in b) for r in per_rank]
+    assert max(loads) / (sum(loads) / 2) < 1.05

@@ -267,8 +267,12 @@ def run_sweep(args):
     gen_frames = [int(n / 25 * SR / 256) for n in n_tok] if not args.from_mu else [int(round(float(d) * SR / HOP)) for d in dur]
     tot = [PROMPT + f for f in gen_frames]
     costs = [shard.utterance_cost(t, f) for t, f in zip(tot, gen_frames)]
-    mine = shard.lpt_assign(costs, world)[rank]
-    batches = shard.make_batches(mine, tot, row_budget=args.row_budget, align=256, max_batch=args.max_batch)
+    if args.shard == "utterance":
+        mine = shard.lpt_assign(costs, world)[rank]
+        batches = shard.make_batches(mine, tot, row_budget=args.row_budget, align=256, max_batch=args.max_batch)
+    else:
+        batches = shard.assign_batches(costs, tot, world, row_budget=args.row_budget, align=256, max_batch=args.max_batch)[rank]
+        mine = [u for b in batches for u in b]
     be = AcousticBackend(synthetic.flow_estimator_sd(False, seed=0), synthetic.hift_sd(False, seed=1), v2=False,
                          dtype=torch.bfloat16, device=dev,
                          frontend_sd=None if args.from_mu else synthetic.flow_frontend_sd(False, seed=2))
@@ -294,10 +298,15 @@ def run_sweep(args):
             else:
                 wavs = be.synthesize_tokens_batch(toks, ptoks, pfeats, embs, zs, sample_rate=SR)
             host = [w.cpu() for w in wavs]
-            one_pass.gpu_s += time.perf_counter() - t_in
+            dt = time.perf_counter() - t_in
+            one_pass.gpu_s += dt
+            one_pass.per_batch.append(dict(n=len(b), max_frames=max(tot[u] for u in b), frames=sum(tot[u] for u in b),
+                                           cost=sum(costs[u] for u in b), model=shard.batch_seconds([tot[u] for u in b], [gen_frames[u] for u in b]),
+                                           seconds=dt))
             n_samples += sum(int(h.shape[-1]) for h in host)
         return n_samples
     one_pass.gpu_s = 0.0
+    one_pass.per_batch = []
 
     def barrier():
         torch.cuda.synchronize()
@@ -306,6 +315,7 @@ def run_sweep(args):
     one_pass()                       # builds programs / graphs per stride bucket
     barrier()
     one_pass.gpu_s = 0.0
+    one_pass.per_batch = []
     n0 = _lib.launch_count()
     t0 = time.perf_counter()
     n_samples = one_pass()
@@ -326,13 +336,16 @@ def run_sweep(args):
         print(json.dumps({
             "config": 5, "workload": f"{args.utterances} utterances, gen 2-30 s + 3 s prompt, v1 flow + HiFT "
                                      f"{'from the encoder output' if args.from_mu else 'from speech tokens (flow.inference + hift.inference)'}, "
-                                     f"utterance-sharded x{world}", "dtype": "bf16", "n_gpus": world,
+                                     f"utterance-sharded x{world} ({args.shard}-level LPT)", "dtype": "bf16", "n_gpus": world,
             "metric": "audio_seconds_per_second", "value": audio_s / t, "seconds": t, "wall_with_input_synthesis": wall,
             "audio_seconds": audio_s, "batches_total": int(sm[3].item()), "cuda_graph": not args.eager,
             "algorithmic_tflop": float(sm[2].item()) / 1e12,
             "frac_of_bf16_peak_per_gpu": float(sm[2].item()) / 1e12 / t / world / tf_peak,
             "rank_imbalance_cost": float(mx[2].item()) * world / float(sm[2].item()),
             "gpu_launches_rank0": _lib.launch_count() - n0}))
+    if args.dump_batches:
+        with open(f"{args.dump_batches}.rank{rank}.json", "w") as f:
+            json.dump(dict(rank=rank, seconds=one_pass.gpu_s, batches=one_pass.per_batch), f)
     if world > 1:
         dist.destroy_process_group()
 
@@ -359,6 +372,9 @@ def main():
     w.add_argument("--row-budget", type=int, default=48 * 1024)
     w.add_argument("--max-batch", type=int, default=64)
     w.add_argument("--eager", action="store_true")
+    w.add_argument("--shard", default="utterance", choices=["batch", "utterance"],
+                   help="batch: whole-job batches, LPT over batch costs (shard.assign_batches); utterance: LPT over utterances, batches per rank")
+    w.add_argument("--dump-batches", default="", help="write per-batch (size, cost, seconds) of the timed pass to <path>.rank<r>.json")
     w.add_argument("--from-mu", action="store_true", help="start at the encoder output (the pre-front-end measurement)")
     args = ap.parse_args()
     _lib.load()
