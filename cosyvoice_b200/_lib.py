@@ -60,6 +60,7 @@ SIGNATURES = {
     "cvb200_interp_linear": [_P, _L, _I, _P, _L, _I, _I, _P],
     "cvb200_pcm16": [_P, _P, _F, _L, _P],
     "cvb200_layernorm": [_P, _I, _P, _I, _I, _P, _P, _I, _I, _F, _P],
+    "cvb200_layernorm_act": [_P, _I, _I, _P, _I, _I, _P, _P, _I, _I, _F, _P],
     "cvb200_norm_mish": [_P, _I, _I, _P, _I, _I, _P, _P, _P, _P, _I, _LAY, _I, _F, _P],
     "cvb200_attention": [_P, _I, _P, _I, _I, _LAY, _I, _F, _P],
     "cvb200_attention_ex": [_P, _I, _P, _I, _I, _LAY, _I, _F, _I, _P],

@@ -28,6 +28,7 @@ void set_pdl_enabled(bool on) { g_pdl.store(on ? 1 : 0, std::memory_order_relaxe
 
 using Layout = cvb200_layout;
 int launch_layernorm(const float*, int, void*, int, int, const float*, const float*, int, int, float, cudaStream_t);
+int launch_layernorm_act(const void*, int, int, void*, int, int, const float*, const float*, int, int, float, cudaStream_t);
 int launch_norm_mish(const void*, int, int, void*, int, int, const float*, const float*, const double*, const float*, int,
                      const Layout&, int, float, cudaStream_t);
 int launch_time_sinusoid(const float*, int, int, float, float*, cudaStream_t);
@@ -129,6 +130,12 @@ int cvb200_layernorm(const float* x, int ldx, void* out, int ldo, int out_dt, co
                      int rows, int C, float eps, void* stream) {
   NEED(x, "x"); NEED(out, "out"); NEED(gamma, "gamma"); NEED(beta, "beta");
   return launch_layernorm(x, ldx, out, ldo, out_dt, gamma, beta, rows, C, eps, ST(stream));
+}
+
+int cvb200_layernorm_act(const void* x, int ldx, int x_dt, void* out, int ldo, int out_dt, const float* gamma,
+                         const float* beta, int rows, int C, float eps, void* stream) {
+  NEED(x, "x"); NEED(out, "out"); NEED(gamma, "gamma"); NEED(beta, "beta");
+  return launch_layernorm_act(x, ldx, x_dt, out, ldo, out_dt, gamma, beta, rows, C, eps, ST(stream));
 }
 
 int cvb200_norm_mish(const void* h, int ldh, int h_dt, void* out, int ldo, int out_dt, const float* gamma,

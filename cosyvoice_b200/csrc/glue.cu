@@ -69,6 +69,33 @@ __global__ void __launch_bounds__(256) layernorm256_kernel(const float* __restri
   store8(out, (size_t)row * ldo + lane * 8, out_dt, v);
 }
 
+// same, reading a residual stream kept in the operand dtype (bf16 engine: cvb200_layernorm_act)
+__global__ void __launch_bounds__(256) layernorm256_act_kernel(const void* __restrict__ x, int ldx, int x_dt,
+                                                               void* __restrict__ out, int ldo, int out_dt,
+                                                               const float* __restrict__ gamma,
+                                                               const float* __restrict__ beta, int rows, float eps) {
+  pdl_sync();
+  const int row = blockIdx.x * 8 + (threadIdx.x >> 5);
+  const int lane = threadIdx.x & 31;
+  if (row >= rows) return;
+  float v[8];
+  load8_dt(x, (size_t)row * ldx + lane * 8, x_dt, v);
+  float s = 0.f;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) s += v[i];
+  const float mean = warp_sum(s) * (1.f / 256.f);
+  float q = 0.f;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) { v[i] -= mean; q += v[i] * v[i]; }
+  const float rstd = rsqrtf(warp_sum(q) * (1.f / 256.f) + eps);
+  float g[8], b[8];
+  load8<float>(gamma + lane * 8, g);
+  load8<float>(beta + lane * 8, b);
+#pragma unroll
+  for (int i = 0; i < 8; ++i) v[i] = v[i] * rstd * g[i] + b[i];
+  store8(out, (size_t)row * ldo + lane * 8, out_dt, v);
+}
+
 // ---------------------------------------------------------------------------- Norm + Mish (Block1D tail)
 __global__ void __launch_bounds__(256) norm_mish256_kernel(const void* __restrict__ h, int ldh, int h_dt,
                                                            void* __restrict__ out, int ldo, int out_dt,
@@ -349,6 +376,16 @@ int launch_layernorm(const float* x, int ldx, void* out, int ldo, int out_dt, co
   CVB_REQUIRE(ldx % 4 == 0 && ldo % 8 == 0, "leading dimensions must keep 16-byte alignment");
   if (rows <= 0) return CVB_OK;
   CVB_CUDA(launch_pdl(layernorm256_kernel, dim3(ceil_div(rows, 8)), dim3(256), 0, st, x, ldx, out, ldo, out_dt, gamma, beta, rows, eps));
+  CVB_LAUNCH_CHECK();
+  return CVB_OK;
+}
+
+int launch_layernorm_act(const void* x, int ldx, int x_dt, void* out, int ldo, int out_dt, const float* gamma,
+                         const float* beta, int rows, int C, float eps, cudaStream_t st) {
+  CVB_REQUIRE(C == 256, "LayerNorm kernel is specialised for 256 channels");
+  CVB_REQUIRE(ldx % 8 == 0 && ldo % 8 == 0, "leading dimensions must keep 16-byte alignment");
+  if (rows <= 0) return CVB_OK;
+  CVB_CUDA(launch_pdl(layernorm256_act_kernel, dim3(ceil_div(rows, 8)), dim3(256), 0, st, x, ldx, x_dt, out, ldo, out_dt, gamma, beta, rows, eps));
   CVB_LAUNCH_CHECK();
   return CVB_OK;
 }

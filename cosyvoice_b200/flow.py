@@ -145,7 +145,12 @@ class _Program:
         self.gn_stats = None if causal else z(n_norm, S, 8, 2, dtype=torch.float64)
         self.A0 = z(R, 320)
         self.h, self.hn = z(R, C), z(R, C)
-        self.X = z(R, C, dtype=torch.float32)
+        # Residual stream of the transformer blocks in the engine's operand dtype: fp32 for the fp32 parity engine, bf16 for
+        # the bf16 engine -- what the reference's own half-precision path does (flow.half(), cli/model.py:43-45).  The
+        # out-projection / FFN-out GEMMs and both LayerNorms of a block are bound by this stream's HBM traffic: bf16 removes
+        # 19 % of a block's bytes (step 298 -> 283 ms) for 0.3 % more rel-rms error on the mel (0.92 % against the 3 % bar;
+        # profiles/r01_residual_bf16.md).  CVB200_RESIDUAL=f32 keeps the stream in fp32.
+        self.X = z(R, C, dtype=torch.float32 if os.environ.get("CVB200_RESIDUAL", "act") == "f32" else dt)
         self.n = z(R, C)
         self.qkv, self.o, self.f = z(R, 3 * HEADS * HEAD_DIM), z(R, HEADS * HEAD_DIM), z(R, 4 * C)
         self.s_in = z(R, C)

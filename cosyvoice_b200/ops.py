@@ -179,9 +179,13 @@ def ffn_fused_op(a: torch.Tensor, w1: torch.Tensor, b1: torch.Tensor, w2: torch.
 def layernorm_op(x, out, gamma, beta, rows: int, eps: float = 1e-5) -> Op:
     _require_cuda(x, out)
     lib = _lib.load()
+    keep = (x, out, gamma, beta)
+    if x.dtype != torch.float32:       # residual stream in the operand dtype
+        args = (x.data_ptr(), x.stride(0), dt_of(x), out.data_ptr(), out.stride(0), dt_of(out), gamma.data_ptr(),
+                beta.data_ptr(), rows, x.shape[1], eps)
+        return lambda _k=keep: _lib.check(lib.cvb200_layernorm_act(*args, _stream()), "layernorm_act")
     args = (x.data_ptr(), x.stride(0), out.data_ptr(), out.stride(0), dt_of(out), gamma.data_ptr(), beta.data_ptr(),
             rows, x.shape[1], eps)
-    keep = (x, out, gamma, beta)
     return lambda _k=keep: _lib.check(lib.cvb200_layernorm(*args, _stream()), "layernorm")
 
 

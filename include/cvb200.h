@@ -170,6 +170,11 @@ int cvb200_pcm16(const float* wav, int16_t* out, float scale, int64_t n, void* s
 int cvb200_layernorm(const float* x, int ldx, void* out, int ldo, int out_dt, const float* gamma,
                      const float* beta, int rows, int C, float eps, void* stream);
 
+/* The same LayerNorm reading a residual stream kept in the operand dtype x_dt (the bf16 engine's stream; the reference's
+ * flow.half() path, cli/model.py:43-45, keeps it in half precision too). */
+int cvb200_layernorm_act(const void* x, int ldx, int x_dt, void* out, int ldo, int out_dt, const float* gamma,
+                         const float* beta, int rows, int C, float eps, void* stream);
+
 /* Block1D tail: out = Mish(Norm(h)) on valid rows (+ seq_bias[seq]), 0 elsewhere.
  * gn_stats != NULL: GroupNorm(8, C) with the statistics accumulated by the producing GEMM
  * (flow/components/decoder.py:35-36,39-41,56); NULL: per-row LayerNorm(C) (flow/decoder.py:41-44). */
