@@ -262,7 +262,7 @@ class _Program:
             self.flops += fl
             self._gemm(t["out"], o, L, X, res=X)
             self.ops.append(ops.layernorm_op(X, n, t["ln3"][0], t["ln3"][1], R))
-            if self.fused_ffn and t["ffw"] is not None and L.m_tiles >= 64:
+            if self.fused_ffn and t["ffw"] is not None and L.m_tiles >= 64 and X.dtype == torch.float32:   # the fused kernel's stream is fp32
                 # FeedForward + residual in one kernel: the [rows, 1024] hidden tensor never goes to HBM
                 fl = (t["ff1"].flops_per_row + t["ff2"].flops_per_row) * sum(L.lens)
                 w1, b1, w2, b2 = t["ffw"]
