@@ -166,6 +166,13 @@ def test_layernorm_and_norm_mish(dtype):
     want = F.layer_norm(X, (256,), g, b)
     tol = 1e-4 if dtype == torch.float32 else 3e-2
     assert (out.float() - want).abs().max().item() < tol
+    if dtype == torch.bfloat16:
+        # cvb200_layernorm_act: the same norm over a residual stream stored in the operand dtype (exact on the same bf16 values)
+        Xb = X.to(dtype)
+        out32 = torch.zeros(lay.rows, 256, device=DEV)
+        ops.layernorm_op(Xb, out32, g, b, lay.rows)()
+        _sync()
+        assert (out32 - F.layer_norm(Xb.float(), (256,), g, b)).abs().max().item() < 1e-4
     # per-row LayerNorm + Mish + time bias (causal Block1D)
     h = X.to(dtype)
     tb = torch.randn(2, 512, device=DEV)[:, 256:]
