@@ -66,6 +66,7 @@ def test_config1_one_full_utterance_fp32_matches_the_oracle():
     want = flow_ref.solve_euler(esd, zs[0], flow_ref.cosine_t_span(10), mu, torch.ones(1, 1, T1 + T2), spks, cond)[:, :, T1:]
     got = _flow(torch.float32).inference_batch(toks, ptoks, pfeats, embs, zs=zs, sample_rate=SR)[0]
     err = (got.cpu() - want).abs().max().item()
+    assert (want - _golden("v1")).abs().max().item() < 1e-4         # the oracle itself against the reference's recording
     gerr = (got.cpu() - _golden("v1")).abs().max().item()
     print(f"full-size flow fp32: max-abs {err:.3e} vs the oracle, {gerr:.3e} vs the reference's recorded mel")
     assert got.shape == (1, 80, T2) and err < 2e-3 and gerr < 2e-3, (err, gerr)
@@ -97,6 +98,7 @@ def test_config3_size_one_full_v2_utterance_fp32_matches_the_oracle():
                             prompt_token_len=i32(ptok.shape[1]), prompt_feat=pfeat.to(DEV), prompt_feat_len=i32(pfeat.shape[1]),
                             embedding=emb.to(DEV), n_timesteps=10, finalize=True)
     err = (got.cpu() - want).abs().max().item()
+    assert (want - _golden("v2")).abs().max().item() < 1e-4         # the oracle itself against the reference's recording
     gerr = (got.cpu() - _golden("v2")).abs().max().item()
     print(f"full-size v2 flow fp32: max-abs {err:.3e} vs the oracle, {gerr:.3e} vs the reference's recorded mel")
     assert got.shape == (1, 80, 500) and err < 2e-3 and gerr < 2e-3, (err, gerr)

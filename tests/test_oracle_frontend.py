@@ -71,6 +71,9 @@ def test_regulator_segments_cover_the_output_once():
         assert pos == l1 + l2 and src == n1 + n2
 
 
+@pytest.mark.skipif(os.environ.get("CVB200_SLOW_TESTS", "0") != "1",
+                    reason="3.4 TFLOP on the host cores (48 s to 3 min here); the same oracle-vs-recording check runs inside "
+                           "tests/test_gpu_fullsize.py on the GPU box, where the oracle mel is computed anyway. CVB200_SLOW_TESTS=1 enables it")
 def test_oracle_at_full_size_matches_the_reference_recording(golden_dir):
     """BASELINE config 1 (v1, 75 prompt + 250 tokens -> T = 281 + 937): the oracle's whole flow.inference against the mel
     the REAL MaskedDiffWithXvec.inference produced (oracle/make_golden.py fullsize()).  The v2 recording of the same
