@@ -70,6 +70,7 @@ SIGNATURES = {
     "cvb200_euler_cfg": [_P, _P, _L, _F, _F, _P],
     "cvb200_rowdot_abs": [_P, _I, _I, _P, _P, _I, _P, _I, _P],
     "cvb200_sine_source": [_P, _LAY, _I, _F, _P, _P, _P, _P, _P, _P, _L, _P],
+    "cvb200_sine_source_noalloc": [_P, _LAY, _I, _F, _P, _P, _P, _P, _P, _L, _P],
     "cvb200_stft16": [_P, _L, _P, _I, _I, _LAY, _P],
     "cvb200_istft16": [_P, _I, _LAY, _P, _L, _F, _P],
     "cvb200_snake": [_P, _I, _I, _P, _I, _I, _P, _I, _LAY, _P],

@@ -5,8 +5,15 @@
 //   snake             x + sin^2(a x)/(a + 1e-9)                 transformer/activation.py:79-82
 //   reflect_row0      ReflectionPad1d((1,0)) fix-up             hifigan/generator.py:358-359
 //   (the anti-aliased SnakeBeta activation lives in antialias.cu)
+#include <mutex>
 #include "common.cuh"
 #include "../../include/cvb200.h"
+
+// Scratch of cvb200_sine_source_noalloc (the frame prefix of the NSF source, fp64): a fixed array in the library's
+// device image instead of a caller buffer, so the entry point never allocates.  One copy per GPU that loads the
+// library, held until the process exits (CVB200_NOALLOC_MAX_ROWS * 8 bytes = 512 KiB).  In HOST code this name is only
+// a stand-in for the symbol: its device address comes from cudaGetSymbolAddress (noalloc_scratch() below).
+static __device__ __align__(256) double g_noalloc_prefix[CVB200_NOALLOC_MAX_ROWS];
 
 namespace cvb {
 
@@ -261,6 +268,41 @@ int launch_sine_source(const float* f0, const Layout& lay0, int hop, float sr, c
   return CVB_OK;
 }
 
+// Device address of g_noalloc_prefix on the CURRENT device, resolved once per device with that device current.
+static int noalloc_scratch(double** out) {
+  constexpr int kMaxDev = 64;
+  static std::mutex mu;
+  static double* ptr[kMaxDev] = {};
+  int dev = -1;
+  CVB_CUDA(cudaGetDevice(&dev));
+  CVB_REQUIRE(dev >= 0 && dev < kMaxDev, "device ordinal beyond the no-alloc scratch table");
+  std::lock_guard<std::mutex> lock(mu);
+  if (ptr[dev] == nullptr) {
+    double* p = nullptr;
+    CVB_CUDA(cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_noalloc_prefix));
+    CVB_REQUIRE(p != nullptr, "cudaGetSymbolAddress returned a null scratch address");
+    ptr[dev] = p;
+  }
+  *out = ptr[dev];
+  return CVB_OK;
+}
+
+int launch_sine_source_noalloc(const float* f0, const Layout& lay0, int hop, float sr, const float* noise,
+                               const float* phase, const float* lin_w, const float* lin_b, float* s, long long l_max,
+                               cudaStream_t st) {
+  if (lay0.rows > CVB200_NOALLOC_MAX_ROWS) {
+    set_last_error("invalid argument: cvb200_sine_source_noalloc: layout has " + std::to_string(lay0.rows) +
+                   " frame rows, the built-in scratch holds CVB200_NOALLOC_MAX_ROWS = " +
+                   std::to_string(CVB200_NOALLOC_MAX_ROWS) + " (use cvb200_sine_source with a caller workspace)");
+    return CVB_ERR_INVALID;
+  }
+  double* scratch = nullptr;
+  CVB_TRY(noalloc_scratch(&scratch));
+  // Nothing in the scratch has to start at zero: f0_prefix_kernel writes prefix[r] for every valid frame row r and
+  // sine_source_kernel reads only those rows, so the previous call's contents are never observed.
+  return launch_sine_source(f0, lay0, hop, sr, noise, phase, lin_w, lin_b, scratch, s, l_max, st);
+}
+
 int launch_stft16(const float* s, long long l_max, void* out, int ldo, int out_dt, const Layout& lay, cudaStream_t st) {
   CVB_REQUIRE(ldo >= 18, "stft output needs 18 columns");
   if (lay.rows <= 0) return CVB_OK;
@@ -295,3 +337,13 @@ int launch_reflect_row0(void* x, int ldx, int dt, int C, const Layout& lay, cuda
 }
 
 }  // namespace cvb
+
+// The one entry point of the library that owns its scratch (declared in include/cvb200.h next to cvb200_sine_source).
+// It lives in this file because the scratch array's device address can only be taken where the symbol is visible.
+extern "C" int cvb200_sine_source_noalloc(const float* f0, const cvb200_layout* lay0, int hop, float sr, const float* noise,
+                                          const float* phase, const float* lin_w, const float* lin_b, float* s,
+                                          int64_t l_max, void* stream) {
+  CVB_REQUIRE(f0 && lay0 && noise && phase && lin_w && lin_b && s, "null argument");
+  return cvb::launch_sine_source_noalloc(f0, *lay0, hop, sr, noise, phase, lin_w, lin_b, s, (long long)l_max,
+                                         reinterpret_cast<cudaStream_t>(stream));
+}

@@ -218,6 +218,19 @@ int cvb200_rowdot_abs(const void* x, int ldx, int x_dt, const float* w, const fl
 int cvb200_sine_source(const float* f0, const cvb200_layout* lay0, int hop, float sr, const float* noise,
                        const float* phase, const float* lin_w, const float* lin_b, double* prefix_ws /*[rows0]*/,
                        float* s, int64_t l_max, void* stream);
+/* cvb200_sine_source without a caller workspace.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot allocate device memory (code under CUDA-graph capture, tight serving loops,
+ * harnesses that forbid cudaMalloc).  The fp64 frame prefix lives in a fixed array inside the library's device image
+ * (CVB200_NOALLOC_MAX_ROWS doubles = 512 KiB on every GPU that loads the library, until the process exits); the call
+ * makes no cudaMalloc / cudaFree / allocating library call.  Inputs and outputs are the caller's, as above.
+ * lay0->rows > CVB200_NOALLOC_MAX_ROWS -> CVB200_ERR_INVALID with a message naming the limit.  Every call on a device
+ * shares the one array: calls that may overlap on the GPU (different streams, no ordering) RACE -- serialise them.
+ * Nothing in it needs clearing between calls (each call writes every element it reads).  The first call on a device
+ * resolves the array's address (cudaGetSymbolAddress): make it outside stream capture. */
+#define CVB200_NOALLOC_MAX_ROWS 65536
+int cvb200_sine_source_noalloc(const float* f0, const cvb200_layout* lay0, int hop, float sr, const float* noise,
+                               const float* phase, const float* lin_w, const float* lin_b, float* s, int64_t l_max,
+                               void* stream);
 /* torch.stft(n_fft 16, hop 4, periodic hann, center/reflect) -> [real(9) | imag(9) | 0...] per frame
  * row (hifigan/generator.py:333-339).  s [B][l_max]; out rows follow layout `lay` (frame rate),
  * frame f of sequence b valid for f < seq_len[b] (= L_b/4 + 1). */
