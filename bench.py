@@ -123,28 +123,75 @@ def cpu_reference_pass(n_timesteps: int = 10):
     return run
 
 
+def physical_cores() -> int:
+    """Physical cores this process may use (SMT siblings do not help the fp32 GEMM/conv kernels of the CPU path)."""
+    try:
+        import psutil
+        n = psutil.cpu_count(logical=False) or 0
+    except Exception:
+        n = 0
+    try:
+        n_aff = len(os.sched_getaffinity(0))
+    except Exception:
+        n_aff = os.cpu_count() or 1
+    if n <= 0 or n > n_aff:
+        n = n_aff
+    return max(1, n)
+
+
+def time_cpu_baseline(flush_denormal: bool, warmup: int, reps: int, threads: int):
+    """Median seconds per utterance of the CPU path: `warmup` untimed runs then `reps` timed ones (BASELINE.md
+    section 3: warm-up 1 + median of 3)."""
+    torch.set_num_threads(threads)
+    torch.set_flush_denormal(flush_denormal)
+    run = cpu_reference_pass()
+    for _ in range(warmup):
+        run()
+    ts = []
+    for _ in range(reps):
+        t0 = time.perf_counter()
+        run()
+        ts.append(time.perf_counter() - t0)
+    return statistics.median(ts), ts
+
+
+def cpu_baseline_no_flush(threads: int, timeout_s: float = 120.0):
+    """The same measurement with denormals NOT flushed (SURVEY.md 8d asks for both; the CFG all-zero branch makes
+    denormals and the survey saw 2.4x to 30x slowdowns), in a child process under a timeout so that an outlier cannot
+    stall the bench."""
+    try:
+        r = subprocess.run([sys.executable, os.path.abspath(__file__), "--impl", "reference", "--steps", "1", "--warmup", "1",
+                            "--no-flush-denormal", "--threads", str(threads)], capture_output=True, text=True,
+                           timeout=timeout_s, env={k: v for k, v in os.environ.items() if k not in ("RANK", "WORLD_SIZE")})
+        for line in r.stdout.splitlines():
+            if line.startswith("{"):
+                return json.loads(line)["value"]
+        return None
+    except subprocess.TimeoutExpired:
+        return f"timeout (> {timeout_s:.0f} s for warm-up 1 + 1 run)"
+    except Exception as e:      # noqa: BLE001 - a reported side measurement must not fail the bench
+        return f"unavailable ({type(e).__name__})"
+
+
+CPU_SAMPLE = ("1 of the batch's utterances per step (325 tokens -> T=1218 frames: front-end, 10 Euler steps with the reference's "
+              "F.scaled_dot_product_attention, HiFT), fp32")
+
+
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    cores = os.cpu_count() or 1
-    torch.set_num_threads(cores)
-    torch.set_flush_denormal(True)      # the CFG all-zero branch produces denormals on CPU
-    run = cpu_reference_pass()
-    for _ in range(args.warmup):
-        run()
-    t0 = time.perf_counter()
-    for _ in range(args.steps):
-        run()
-    dt = (time.perf_counter() - t0) / args.steps
+    cores = args.threads or physical_cores()
+    flush = not args.no_flush_denormal
+    dt, raw = time_cpu_baseline(flush, args.warmup, args.steps, cores)
     val = audio_seconds(1) / dt
-    sample = ("1 of the batch's utterances per step (325 tokens -> T=1218 frames: front-end, 10 Euler steps, HiFT), fp32, "
-              "flush_denormal on")
+    sample = CPU_SAMPLE + f", median of {args.steps} after {args.warmup} warm-up, {cores} threads, flush_denormal {'on' if flush else 'off'}"
     print(json.dumps({
         "impl": "reference", "metric": "audio_seconds_per_second", "value": val, "unit": "audio-s/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": WORKLOAD.format(b=args.batch), "sample": sample},
+        "config": {"workload": WORKLOAD.format(b=args.batch), "sample": sample, "threads": cores,
+                   "logical_cpus": os.cpu_count(), "s_per_utterance_runs": raw},
         "cpu_baseline": {"value": val, "unit": "audio-s/s", "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": val, "unit": "audio-s/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }))
@@ -289,17 +336,14 @@ def run_ours(args):
                                    "ms": att["ms"], "achieved_tflops": att["flops"] / (att["ms"] * 1e-3) / 1e12,
                                    "share_of_eager_step": att["ms"] / prof["_step_ms_eager"]}},
     }
-    if world == 1:
-        cores = os.cpu_count() or 1
-        torch.set_num_threads(cores)
-        torch.set_flush_denormal(True)
-        run = cpu_reference_pass()
-        t0 = time.perf_counter()
-        run()
-        dt = time.perf_counter() - t0
+    if world == 1 and not args.no_cpu_baseline:
+        cores = physical_cores()
+        dt, raw = time_cpu_baseline(True, 1, 3, cores)
         out["cpu_baseline"] = {"value": audio_seconds(1) / dt, "unit": "audio-s/s", "cores": cores, "kind": "port",
-                               "sample": "1 utterance of the batch (325 tokens -> T=1218: front-end, 10 Euler steps, HiFT), "
-                                         "single cold run, fp32, flush_denormal on"}
+                               "sample": CPU_SAMPLE + f", warm-up 1 + median of 3, {cores} threads (physical cores), "
+                                                      "flush_denormal on",
+                               "s_per_utterance_runs": raw,
+                               "value_no_flush_denormal": cpu_baseline_no_flush(cores)}
     print(json.dumps(out))
     if world > 1:
         dist.destroy_process_group()
@@ -312,6 +356,9 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--batch", type=int, default=32)
+    ap.add_argument("--threads", type=int, default=0, help="CPU arm: torch threads (default: physical cores)")
+    ap.add_argument("--no-flush-denormal", action="store_true", help="CPU arm: leave denormals on")
+    ap.add_argument("--no-cpu-baseline", action="store_true", help="B200 arm: skip the cpu_baseline leg (kernel iteration)")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

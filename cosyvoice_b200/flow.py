@@ -325,14 +325,17 @@ class B200Estimator:
         """Programs are cached per STRIDE pattern (lengths are device data, re-bound in place), so a streaming
         session whose T grows chunk by chunk reuses one program / CUDA graph per 128-row bucket."""
         key = lay.stride_key()
-        p = self._programs.get(key)
+        p = self._programs.pop(key, None)
         if p is None:
             if len(self._programs) >= 32:
-                self._programs.pop(next(iter(self._programs))).release()
+                # LRU: the dict is kept in use order (hits are re-inserted below).  The evicted program is only dropped
+                # from the cache, not torn down: holders of a reference (AcousticBackend.prepare_resident*, a captured
+                # CUDA graph) keep a consistent object and its HBM is returned when the last reference goes.
+                self._programs.pop(next(iter(self._programs)))
             p = _Program(self.weights, SeqLayout(lay.lens, lay.strides, self.device), self.engine)
-            self._programs[key] = p
         else:
             p.set_lens(lay.lens)
+        self._programs[key] = p
         return p
 
     @torch.inference_mode()
@@ -438,8 +441,10 @@ class B200ConditionalCFM:
         if not self.use_cuda_graph:
             self._steps(prog, st, ts, dts)
             return
-        key = (lay1.stride_key(), n_timesteps)
-        g = self._graphs.get(key)
+        # the captured launches bake in the schedule and the CFG rate: both are part of the key, so that changing
+        # cfm.inference_cfg_rate / t_scheduler after the first solve re-captures instead of being silently ignored
+        key = (lay1.stride_key(), n_timesteps, float(self.inference_cfg_rate), self.t_scheduler)
+        g = self._graphs.pop(key, None)
         if g is not None and g[1] is not prog:      # the program of this bucket was evicted and rebuilt
             g = None
         if g is None:
@@ -453,15 +458,16 @@ class B200ConditionalCFM:
             st["x"].copy_(keep)
             graph = torch.cuda.CUDAGraph()
             n0 = _lib.launch_count()
-            with torch.cuda.graph(graph):
+            # thread_local: other session threads (front-end, HiFT, the LLM thread) may allocate or copy while this
+            # thread captures; in the default "global" mode their calls would fail and invalidate the capture
+            with torch.cuda.graph(graph, capture_error_mode="thread_local"):
                 self._steps(prog, st, ts, dts)
             n_launch = _lib.launch_count() - n0
             st["x"].copy_(keep)
             if len(self._graphs) >= 32:
-                self._graphs.pop(next(iter(self._graphs)))
-            self._graphs = {k: v for k, v in self._graphs.items() if v[1].__dict__}     # drop graphs of released programs
+                self._graphs.pop(next(iter(self._graphs)))          # least recently used
             g = (graph, prog, n_launch)
-            self._graphs[key] = g
+        self._graphs[key] = g                                        # (re-)insert at the most-recent end
         self.last_graph_launches = g[2]
         g[0].replay()
 

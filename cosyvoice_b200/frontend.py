@@ -314,12 +314,12 @@ class _FlowBase:
     def _program(self, tok: SeqLayout, mel: SeqLayout) -> _Program:
         chunk = int(self.encoder.static_chunk_size)
         key = (tok.stride_key(), mel.stride_key(), chunk)
-        p = self._programs.get(key)
+        p = self._programs.pop(key, None)
         if p is None:
             if len(self._programs) >= 32:
-                self._programs.pop(next(iter(self._programs))).release()
+                self._programs.pop(next(iter(self._programs)))      # LRU; holders of the evicted program keep it alive
             p = _Program(self.weights, tok, mel, self.engine, chunk)
-            self._programs[key] = p
+        self._programs[key] = p
         return p
 
     @torch.inference_mode()

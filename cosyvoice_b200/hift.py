@@ -119,7 +119,8 @@ class _Weights:
 class _Program:
     """Launch list + buffers of one batched HiFT forward over a fixed set of mel lengths."""
 
-    def __init__(self, w: _Weights, lens: Sequence[int], engine: int, strides: Optional[Sequence[int]] = None):
+    def __init__(self, w: _Weights, lens: Sequence[int], engine: int, strides: Optional[Sequence[int]] = None,
+                 sampling_rate: float = 24000.0, audio_limit: float = 0.99):
         self.w, self.engine = w, engine
         dev, dt = w.device, w.dtype
         self.lens = [int(l) for l in lens]
@@ -189,7 +190,7 @@ class _Program:
         self.ops_f0.append(lambda: ops.rowdot_abs(f0_in, w.f0_w, w.f0_b, self.f0, R0))
         # ---- source: f0 -> s (generator.py:404-406)
         self.ops_src: List[ops.Op] = [
-            lambda: ops.sine_source(self.f0, lay0, w.hop, 24000.0, self.noise, self.phase, w.src_w, w.src_b,
+            lambda: ops.sine_source(self.f0, lay0, w.hop, float(sampling_rate), self.noise, self.phase, w.src_w, w.src_b,
                                     self.prefix, self.s)]
         # ---- decode (generator.py:349-381)
         self.ops.append(lambda: ops.stft16(self.s, self.sst, lay_f))
@@ -232,7 +233,7 @@ class _Program:
         self.cp = z(lay_f.rows, 32, dtype=f32)
         self._gemm(w.conv_post, x_prev, lay_f, self.cp)
         self.marks["conv_post"] = (len(self.ops), self.cp, lay_f)
-        self.ops.append(lambda: ops.istft16(self.cp, lay_f, self.wav, 0.99))
+        self.ops.append(lambda: ops.istft16(self.cp, lay_f, self.wav, float(audio_limit)))
 
     def release(self):
         """Drop buffers and launch closures (they reference each other in cycles: without this an evicted program
@@ -291,7 +292,8 @@ class B200HiFTGenerator:
             engine = _lib.ENGINE_TCGEN05 if dtype == torch.bfloat16 else _lib.ENGINE_SIMT
         self.engine, self.dtype, self.v2 = engine, dtype, v2
         self.weights = _Weights(sd, v2, dtype, self.device)
-        self.sampling_rate = sampling_rate
+        self.sampling_rate = sampling_rate      # SineGen's F = f0 / sampling_rate (hifigan/generator.py:146-148)
+        self.audio_limit = audio_limit          # final clamp (generator.py:380)
         self.hop = self.weights.hop
         self._programs: Dict[tuple, _Program] = {}
         self.serial = ops.Serial()          # cached programs are shared scratch: one user (thread / stream) at a time
@@ -304,14 +306,15 @@ class B200HiFTGenerator:
         key = tuple((l + 8 + 127) // 128 * 128 for l in lens)
         if uniform_stride:
             key = (max(key),) * len(key)
-        p = self._programs.get(key)
+        p = self._programs.pop(key, None)
         if p is None:
             if len(self._programs) >= 8:
-                self._programs.pop(next(iter(self._programs))).release()
-            p = _Program(self.weights, lens, self.engine, strides=key)
-            self._programs[key] = p
+                self._programs.pop(next(iter(self._programs)))      # LRU; holders of the evicted program keep it alive
+            p = _Program(self.weights, lens, self.engine, strides=key, sampling_rate=float(self.sampling_rate),
+                         audio_limit=float(self.audio_limit))
         else:
             p.set_lens(lens)
+        self._programs[key] = p
         return p
 
     def draw_source_rng(self, prog: _Program):

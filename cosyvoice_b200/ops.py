@@ -19,8 +19,9 @@ from .packing import TapPlan
 Op = Callable[[], None]
 
 
-import os as _os
-_NO_SERIAL = _os.environ.get("CVB200_NO_SERIAL", "0") == "1"
+# Test-only A/B switch (tests/test_gpu_concurrency.py monkeypatches it to show the race it guards against).  Deliberately
+# NOT an environment variable: a leaked variable must not be able to switch the protection off in production.
+_NO_SERIAL = False
 
 
 class Serial:
@@ -35,20 +36,26 @@ class Serial:
         self._event: Optional[torch.cuda.Event] = None
 
     def __enter__(self):
-        if _NO_SERIAL:                  # CVB200_NO_SERIAL=1: A/B switch that shows tests/test_gpu_concurrency.py failing
+        if _NO_SERIAL:
             return self
         self._lock.acquire()
-        if self._event is not None:
-            torch.cuda.current_stream().wait_event(self._event)
+        try:
+            if self._event is not None:
+                torch.cuda.current_stream().wait_event(self._event)
+        except BaseException:           # e.g. the caller's stream is capturing: never leave the lock held
+            self._lock.release()
+            raise
         return self
 
     def __exit__(self, *exc):
         if _NO_SERIAL:
             return False
-        ev = torch.cuda.Event()
-        ev.record()
-        self._event = ev
-        self._lock.release()
+        try:
+            ev = torch.cuda.Event()
+            ev.record()
+            self._event = ev
+        finally:
+            self._lock.release()
         return False
 
 # bench.py's roofline leg: when a list is installed here, every GEMM / attention launch is bracketed by CUDA

@@ -80,8 +80,24 @@ def _resnet(sd: SD, p: str, x, mask, temb, causal):
 
 # ----------------------------------------------------------------------------- transformer
 def _attention(sd: SD, p: str, x, attn_mask):
-    """diffusers 0.27.2 Attention + AttnProcessor2_0, written out explicitly
-    (softmax(QK^T * d^-1/2 + M) V; the float mask M is ADDED, flow/decoder.py:258)."""
+    """diffusers 0.27.2 Attention + AttnProcessor2_0 as the reference reaches it (components/transformer.py:196-204,
+    266-271): prepare_attention_mask repeats the float mask per head, then ONE F.scaled_dot_product_attention call
+    (softmax(QK^T * d^-1/2 + M) V; the float mask M is ADDED, flow/decoder.py:258).  Calling SDPA -- not an explicit
+    matmul/softmax/matmul -- matters for the CPU baseline: it is the reference's own cost (round-1 review: the explicit
+    form was 1.55x slower on the flow)."""
+    B, S, _ = x.shape
+    q = F.linear(x, sd[p + "to_q.weight"]).view(B, S, N_HEADS, HEAD_DIM).transpose(1, 2)
+    k = F.linear(x, sd[p + "to_k.weight"]).view(B, S, N_HEADS, HEAD_DIM).transpose(1, 2)
+    v = F.linear(x, sd[p + "to_v.weight"]).view(B, S, N_HEADS, HEAD_DIM).transpose(1, 2)
+    if attn_mask is not None:
+        attn_mask = attn_mask.repeat_interleave(N_HEADS, dim=0).view(B, N_HEADS, -1, attn_mask.shape[-1])
+    o = F.scaled_dot_product_attention(q, k, v, attn_mask=attn_mask, dropout_p=0.0, is_causal=False)
+    o = o.transpose(1, 2).reshape(B, S, N_HEADS * HEAD_DIM)
+    return F.linear(o, sd[p + "to_out.0.weight"], sd[p + "to_out.0.bias"])
+
+
+def _attention_explicit(sd: SD, p: str, x, attn_mask):
+    """The same attention written out (independent cross-check of the SDPA call, SURVEY.md 8c last row)."""
     B, S, _ = x.shape
     q = F.linear(x, sd[p + "to_q.weight"]).view(B, S, N_HEADS, HEAD_DIM).transpose(1, 2)
     k = F.linear(x, sd[p + "to_k.weight"]).view(B, S, N_HEADS, HEAD_DIM).transpose(1, 2)

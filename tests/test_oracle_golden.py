@@ -113,3 +113,22 @@ def test_token2wav_oracle_matches_reference_session(golden_dir, ver):
         assert torch.equal(o, ref), f"chunk {i}"                    # fades are double -> fp32, stubs dyadic: bit-exact
     for k, v in d["state"].items():
         assert torch.equal(state[k], v) if torch.is_tensor(v) else tuple(state[k]) == tuple(v), k
+
+
+def test_sdpa_attention_of_the_port_equals_the_written_out_form():
+    """oracle/flow_ref._attention calls F.scaled_dot_product_attention the way diffusers' AttnProcessor2_0 does (so the CPU
+    baseline costs what the reference costs); the explicit softmax(QK^T d^-1/2 + M) V form is the independent cross-check
+    SURVEY.md 8c asks for.  Includes a mask with padded keys: the {0,1} float mask is ADDED, not applied as a boolean."""
+    import torch
+    from oracle import flow_ref, init_weights
+    sd = init_weights.flow_estimator_sd(False, seed=0)
+    p = "mid_blocks.3.1.2.attn1."
+    g = torch.Generator().manual_seed(5)
+    x = torch.randn(2, 37, 256, generator=g)
+    mask = torch.ones(2, 1, 37)
+    mask[1, :, 30:] = 0
+    am = torch.matmul(mask.transpose(1, 2), mask)
+    a = flow_ref._attention(sd, p, x, am)
+    b = flow_ref._attention_explicit(sd, p, x, am)
+    assert (a - b).abs().max().item() < 2e-5
+    assert (flow_ref._attention(sd, p, x, None) - flow_ref._attention_explicit(sd, p, x, None)).abs().max().item() < 2e-5
