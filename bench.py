@@ -332,6 +332,9 @@ def run_ours(args):
                      "hbm_gbps_from_traffic": (traffic * tc["launches"] / (tc["ms"] * 1e-3) / 1e9) if traffic else None,
                      "launches_per_step": tc["launches"], "kernel_ms_per_step": tc["ms"],
                      "share_of_eager_step": tc["ms"] / prof["_step_ms_eager"],
+                     "kernels": {k: {"launches": d["launches"], "ms": round(d["ms"], 3),
+                                     "tflops": round(d["flops"] / max(d["ms"], 1e-9) / 1e9, 1)}
+                                 for k, d in prof.items() if isinstance(d, dict)},
                      "attention": {"kernel": "attention_tc_kernel (tcgen05/TMEM flash)", "launches": att["launches"],
                                    "ms": att["ms"], "achieved_tflops": att["flops"] / (att["ms"] * 1e-3) / 1e12,
                                    "share_of_eager_step": att["ms"] / prof["_step_ms_eager"]}},

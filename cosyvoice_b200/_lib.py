@@ -27,6 +27,7 @@ class Epilogue(C.Structure):
         ("ldr", C.c_int32), ("res_dt", C.c_int32), ("out_scale", C.c_float), ("accumulate", C.c_int32),
         ("ldo0", C.c_int32), ("out0_dt", C.c_int32), ("phase_col", C.c_int32), ("out1_mode", C.c_int32),
         ("ldo1", C.c_int32), ("out1_dt", C.c_int32), ("out1_slope", C.c_float), ("gn_groups", C.c_int32),
+        ("row_stats", C.c_void_p), ("row_u", C.c_void_p),
     ]
 
 
@@ -55,6 +56,7 @@ _LAY = C.POINTER(Layout)
 SIGNATURES = {
     "cvb200_tapgemm": [C.POINTER(Gemm), _I, _P],
     "cvb200_ffn_fused": [_P, _I, _P, _P, _P, _P, _P, _I, _P, _I, _LAY, _P],
+    "cvb200_block_ffn": [_P, _I, _F, _P, _P, _P, _P, _P, _P, _I, _P, _LAY, _P],
     "cvb200_split3_bf16": [_P, _I, _I, _I, _P, _I, _L, _P],
     "cvb200_fade_in_out": [_P, _L, _I, _P, _L, _I, _P, _I, _I, _P],
     "cvb200_interp_linear": [_P, _L, _I, _P, _L, _I, _I, _P],

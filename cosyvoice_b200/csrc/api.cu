@@ -48,6 +48,8 @@ int launch_snake(const void*, int, int, void*, int, int, const float*, int, cons
 int launch_reflect_row0(void*, int, int, int, const Layout&, cudaStream_t);
 int launch_ffn_fused(const void*, int, const void*, const float*, const void*, const float*, float*, int, void*, int,
                      const cvb200_layout&, cudaStream_t);
+int launch_block_ffn(void*, int, float, const void*, const float*, const float*, const void*, const float*, void*, int, float*,
+                     const cvb200_layout&, cudaStream_t);
 int launch_split3_bf16(const float*, int, int, int, void*, int, long long, cudaStream_t);
 int launch_fade_in_out(float*, long long, int, const float*, long long, int, const double*, int, int, cudaStream_t);
 int launch_interp_linear(const float*, long long, int, float*, long long, int, int, cudaStream_t);
@@ -69,8 +71,8 @@ int launch_l2_normalize(const float*, float*, int, int, cudaStream_t);
 
 using namespace cvb;
 // the ctypes mirror in cosyvoice_b200/_lib.py relies on this layout (tests/test_lib_cpu.py)
-static_assert(sizeof(cvb200_epilogue) == 128, "cvb200_epilogue layout");
-static_assert(sizeof(cvb200_gemm) == 352, "cvb200_gemm layout");
+static_assert(sizeof(cvb200_epilogue) == 144, "cvb200_epilogue layout");
+static_assert(sizeof(cvb200_gemm) == 368, "cvb200_gemm layout");
 static_assert(sizeof(cvb200_layout) == 48, "cvb200_layout layout");
 #define ST(s) reinterpret_cast<cudaStream_t>(s)
 #define NEED(p, what)                                                                    \
@@ -106,6 +108,12 @@ int cvb200_ffn_fused(const void* a, int lda, const void* w1, const float* b1, co
                      int ldx, void* out1, int ldo1, const cvb200_layout* lay, void* stream) {
   CVB_REQUIRE(lay != nullptr, "null layout");
   return launch_ffn_fused(a, lda, w1, b1, w2, b2, x, ldx, out1, ldo1, *lay, ST(stream));
+}
+
+int cvb200_block_ffn(void* x, int ldx, float eps, const void* w1f, const float* u1, const float* b1f, const void* w2,
+                     const float* b2, void* out1, int ldo1, float* stats_out, const cvb200_layout* lay, void* stream) {
+  CVB_REQUIRE(lay != nullptr, "null layout");
+  return launch_block_ffn(x, ldx, eps, w1f, u1, b1f, w2, b2, out1, ldo1, stats_out, *lay, ST(stream));
 }
 
 int cvb200_split3_bf16(const float* x, int ldx, int C, int cpad, void* out, int ldo, int64_t rows, void* stream) {

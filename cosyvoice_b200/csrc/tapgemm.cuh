@@ -202,6 +202,13 @@ template <int NV, bool PRECISE>
 __device__ __forceinline__ void epi_apply(const Epi& e, size_t m, int b, bool valid, int phase, int n0, float (&v)[NV],
                                           float& gsum, float& gsq) {
   static_assert(NV % 4 == 0, "chunk must be a multiple of 4 columns");
+  if (e.row_stats) {                   // folded LayerNorm: per-row scale and rank-1 mean correction (include/cvb200.h)
+    const float2 rs = __ldg(reinterpret_cast<const float2*>(e.row_stats) + m);
+    float u[NV];
+    vec_load_f32<NV>(e.row_u + n0, u);
+#pragma unroll
+    for (int j = 0; j < NV; ++j) v[j] = fmaf(v[j], rs.x, rs.y * u[j]);
+  }
   if (e.bias) vec_add_f32<NV>(e.bias + n0, v);
   if (e.seq_bias) vec_add_f32<NV>(e.seq_bias + (size_t)b * e.seq_bias_ld + n0, v);
   if (e.act != ACT_NONE) {
@@ -274,6 +281,8 @@ inline int check_epilogue_layout(const GemmParams& p) {
   CVB_REQUIRE(!e.seq_bias || (al16(e.seq_bias) && e.seq_bias_ld % 4 == 0), "seq_bias alignment");
   CVB_REQUIRE(e.act != ACT_SNAKE || (e.act_alpha && al16(e.act_alpha)), "act_alpha alignment");
   CVB_REQUIRE(!e.gn_stats || (p.N % 32 == 0 && e.gn_groups == p.N / 32), "GroupNorm statistics need N % 32 == 0");
+  CVB_REQUIRE(!e.row_stats || (e.row_u && al16(e.row_u) && (reinterpret_cast<uintptr_t>(e.row_stats) & 7) == 0 && p.n_phase == 1),
+              "row_stats needs row_u (16-byte aligned, n_pad long), 8-byte aligned statistics and a single phase");
   return CVB_OK;
 }
 

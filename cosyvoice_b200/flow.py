@@ -21,7 +21,7 @@ import torch
 
 from . import _lib, ops
 from .layout import SeqLayout
-from .packing import TapPlan, conv1d_plan, conv_transpose1d_plan, linear_plan
+from .packing import TapPlan, conv1d_plan, conv_transpose1d_plan, folded_linear_plan, linear_plan
 
 SD = Dict[str, torch.Tensor]
 C = 256           # estimator width
@@ -41,15 +41,17 @@ class _Weights:
 
     @staticmethod
     def _ffn_weights(sd: SD, p: str, dtype, device):
-        """Operands of the fused FeedForward kernel (bf16 engine only): plain nn.Linear layouts."""
+        """Operands of the fused second half of a block (bf16 engine only, csrc/block_ffn_tc.cu): norm3 folded into the
+        FFN-in weights (ops.fold_layernorm), FFN-out in its nn.Linear layout."""
         if dtype != torch.bfloat16:
             return None
         w1, w2 = sd[p + "ff.net.0.proj.weight"], sd[p + "ff.net.2.weight"]
         if tuple(w1.shape) != (1024, 256) or tuple(w2.shape) != (256, 1024):
             return None
         dev = lambda t, dt: t.detach().to(device=device, dtype=dt).contiguous()
-        return (dev(w1, torch.bfloat16), dev(sd[p + "ff.net.0.proj.bias"], torch.float32),
-                dev(w2, torch.bfloat16), dev(sd[p + "ff.net.2.bias"], torch.float32))
+        w1f, u1, b1f = ops.fold_layernorm(w1.to(device), sd[p + "ff.net.0.proj.bias"], sd[p + "norm3.weight"],
+                                          sd[p + "norm3.bias"], torch.bfloat16)
+        return (w1f, u1, b1f, dev(w2, torch.bfloat16), dev(sd[p + "ff.net.2.bias"], torch.float32))
 
     def __init__(self, sd: SD, causal: bool, dtype: torch.dtype, device):
         self.causal, self.dtype, self.device = causal, dtype, device
@@ -81,6 +83,10 @@ class _Weights:
             wqkv = torch.cat([sd[p + "attn1.to_q.weight"], sd[p + "attn1.to_k.weight"], sd[p + "attn1.to_v.weight"]], 0)
             return dict(ln1=(f32(p + "norm1.weight"), f32(p + "norm1.bias")),
                         qkv=linear_plan(wqkv, None, dtype, device),
+                        # norm1 folded into the QKV projection: used when the previous block's fused kernel left the row
+                        # statistics of the stream (bf16 engine)
+                        qkv_f=(folded_linear_plan(wqkv, None, sd[p + "norm1.weight"], sd[p + "norm1.bias"], dtype, device)
+                               if dtype == torch.bfloat16 else None),
                         out=linear_plan(sd[p + "attn1.to_out.0.weight"], sd[p + "attn1.to_out.0.bias"], dtype, device),
                         ln3=(f32(p + "norm3.weight"), f32(p + "norm3.bias")),
                         ff1=linear_plan(sd[p + "ff.net.0.proj.weight"], sd[p + "ff.net.0.proj.bias"], dtype, device),
@@ -130,10 +136,9 @@ class _Program:
         self.w, self.lay, self.engine = w, lay, engine
         dev, dt = w.device, w.dtype
         causal = w.causal
-        # Fused FeedForward kernel (csrc/ffn_tc.cu): parity-tested, 152 us against 187 us for the unfused pair when
-        # timed alone with a cold L2, but inside the solve the unfused pair finds most of its hidden tensor in L2 and
-        # the step time is the same: opt-in until its output drain overlaps the next tile.
-        self.fused_ffn = engine == _lib.ENGINE_TCGEN05 and os.environ.get("CVB200_FUSED_FFN", "0") == "1"
+        # Fused second half of a transformer block (csrc/block_ffn_tc.cu): norm3 + FeedForward + residual (+ the next
+        # block's norm1) in one kernel on the bf16 residual stream.  CVB200_FUSED_FFN=0 restores the four separate launches.
+        self.fused_ffn = engine == _lib.ENGINE_TCGEN05 and os.environ.get("CVB200_FUSED_FFN", "1") == "1"
         R, S = lay.rows, lay.n_seq
         z = lambda *shape, dtype=dt: torch.zeros(*shape, dtype=dtype, device=dev)
         self.t = z(S, dtype=torch.float32)
@@ -152,6 +157,7 @@ class _Program:
         # profiles/r01_residual_bf16.md).  CVB200_RESIDUAL=f32 keeps the stream in fp32.
         self.X = z(R, C, dtype=torch.float32 if os.environ.get("CVB200_RESIDUAL", "act") == "f32" else dt)
         self.n = z(R, C)
+        self.row_stats = z(R, 2, dtype=torch.float32)       # (rstd, -mean rstd) of the stream's rows, left by block_ffn
         self.qkv, self.o, self.f = z(R, 3 * HEADS * HEAD_DIM), z(R, HEADS * HEAD_DIM), z(R, 4 * C)
         self.s_in = z(R, C)
         self.fin = z(R, C)
@@ -253,25 +259,35 @@ class _Program:
         if r["index"] == 0:
             self.taps["down0.resnet"] = (self.X, L)
         qkv, o, f = self.qkv[:R], self.o[:R], self.f[:R]
+        n_tb = len(st["tbs"])
+        # Fused second half (norm3 + FFN + residual, one kernel).  Chosen by the engine only, never by the problem size: a
+        # batch member must equal its own B = 1 run bit for bit (tests/test_gpu_fullsize.py), so both take the same kernels.
+        fuse = self.fused_ffn and X.dtype == torch.bfloat16 and all(t["ffw"] is not None for t in st["tbs"])
+        stats = self.row_stats[:R]
         for k, t in enumerate(st["tbs"]):
             # components/transformer.py:262-316
-            self.ops.append(ops.layernorm_op(X, n, t["ln1"][0], t["ln1"][1], R))
-            self._gemm(t["qkv"], n, L, qkv, bias=False)
+            last = k == n_tb - 1
+            if fuse and k > 0:
+                # norm1 folded into the projection: the previous block's kernel left (rstd, -mean rstd) of every row
+                pf = t["qkv_f"]
+                self._gemm(pf, X, L, qkv, row_stats=stats, row_u=pf.extra["row_u"])
+            else:
+                self.ops.append(ops.layernorm_op(X, n, t["ln1"][0], t["ln1"][1], R))
+                self._gemm(t["qkv"], n, L, qkv, bias=False)
             fl = sum(4 * HEADS * HEAD_DIM * l * l for l in L.lens)
             self.ops.append(ops.attention_op(qkv, o, L, HEADS, HEAD_DIM ** -0.5, flops=fl))
             self.flops += fl
             self._gemm(t["out"], o, L, X, res=X)
-            self.ops.append(ops.layernorm_op(X, n, t["ln3"][0], t["ln3"][1], R))
-            if self.fused_ffn and t["ffw"] is not None and L.m_tiles >= 64 and X.dtype == torch.float32:   # the fused kernel's stream is fp32
-                # FeedForward + residual in one kernel: the [rows, 1024] hidden tensor never goes to HBM
+            if fuse:
                 fl = (t["ff1"].flops_per_row + t["ff2"].flops_per_row) * sum(L.lens)
-                w1, b1, w2, b2 = t["ffw"]
-                self.ops.append(ops.ffn_fused_op(n, w1, b1, w2, b2, X, L, flops=fl,
-                                                 out1=last_copy if k == len(st["tbs"]) - 1 else None))
+                w1f, u1, b1f, w2, b2 = t["ffw"]
+                self.ops.append(ops.block_ffn_op(X, w1f, u1, b1f, w2, b2, L, flops=fl, out1=last_copy if last else None,
+                                                 stats_out=None if last else stats))
                 self.flops += fl
                 continue
+            self.ops.append(ops.layernorm_op(X, n, t["ln3"][0], t["ln3"][1], R))
             self._gemm(t["ff1"], n, L, f, act=_lib.ACT_GELU)
-            if k == len(st["tbs"]) - 1:
+            if last:
                 self._gemm(t["ff2"], f, L, X, res=X, out1=last_copy, out1_mode=_lib.OUT1_COPY)
             else:
                 self._gemm(t["ff2"], f, L, X, res=X)

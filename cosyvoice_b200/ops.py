@@ -109,7 +109,8 @@ def gemm_op(plan: TapPlan, A: torch.Tensor, lay: SeqLayout, out0: torch.Tensor, 
             res: Optional[torch.Tensor] = None, out_scale: float = 1.0, accumulate: bool = False,
             out1: Optional[torch.Tensor] = None, out1_mode: int = _lib.OUT1_NONE,
             out1_alpha: Optional[torch.Tensor] = None, out1_slope: float = 0.0,
-            gn_stats: Optional[torch.Tensor] = None, flops: int = 0) -> Op:
+            gn_stats: Optional[torch.Tensor] = None, row_stats: Optional[torch.Tensor] = None,
+            row_u: Optional[torch.Tensor] = None, flops: int = 0) -> Op:
     """A: 2-D time-major tensor (possibly a column slice view) whose rows follow the layout of the
     INPUT signal; `lay` is the M-space layout (output rows / n_phase).  out0/out1/res: 2-D tensors
     whose row r, column block [phase*phase_col, +N) receive M-row r of that phase."""
@@ -156,8 +157,12 @@ def gemm_op(plan: TapPlan, A: torch.Tensor, lay: SeqLayout, out0: torch.Tensor, 
     if gn_stats is not None:
         assert gn_stats.dtype == torch.float64
         e.gn_stats, e.gn_groups = gn_stats.data_ptr(), plan.N // 32
+    if row_stats is not None:        # folded LayerNorm (include/cvb200.h): A holds the raw rows, W = W * gamma
+        assert row_stats.dtype == torch.float32 and row_stats.is_contiguous() and row_stats.shape[-1] == 2
+        assert row_u is not None and row_u.dtype == torch.float32 and row_u.numel() >= plan.n_pad
+        e.row_stats, e.row_u = row_stats.data_ptr(), row_u.data_ptr()
     lib = _lib.load()
-    keep = (plan, A, lay, out0, seq_len, out_limit, seq_bias, act_alpha, res, out1, out1_alpha, gn_stats)
+    keep = (plan, A, lay, out0, seq_len, out_limit, seq_bias, act_alpha, res, out1, out1_alpha, gn_stats, row_stats, row_u)
 
     def run(_g=g, _keep=keep):
         _lib.check(lib.cvb200_tapgemm(C.byref(_g), engine, _stream()), "tapgemm")
@@ -181,6 +186,43 @@ def ffn_fused_op(a: torch.Tensor, w1: torch.Tensor, b1: torch.Tensor, w2: torch.
     def launch(_keep=keep):
         _lib.check(lib.cvb200_ffn_fused(*args, _stream()), "ffn_fused")
     return _profiled("gemm", flops, launch)
+
+
+def fold_layernorm(w: torch.Tensor, b: Optional[torch.Tensor], gamma: torch.Tensor, beta: torch.Tensor, dtype):
+    """LayerNorm folded into the Linear that consumes it: W . LN(x) + b = rstd (Wf . x) - rstd mean u + bf with
+    Wf = W * gamma (rounded to the operand dtype), u = rowsum(Wf) of the ROUNDED weights (so that the mean term cancels
+    exactly), bf = b + W . beta.  Returns (Wf [N, K] in `dtype`, u [N] fp32, bf [N] fp32) on w's device."""
+    w32, g32, be32 = w.detach().float(), gamma.detach().float().to(w.device), beta.detach().float().to(w.device)
+    wf = (w32 * g32[None, :]).to(dtype)
+    u = wf.float().sum(dim=1)
+    bf = w32 @ be32
+    if b is not None:
+        bf = bf + b.detach().float().to(w.device)
+    return wf.contiguous(), u.contiguous(), bf.contiguous()
+
+
+def block_ffn_op(x: torch.Tensor, w1f: torch.Tensor, u1: torch.Tensor, b1f: torch.Tensor, w2: torch.Tensor, b2: torch.Tensor,
+                 lay: SeqLayout, out1: Optional[torch.Tensor] = None, stats_out: Optional[torch.Tensor] = None,
+                 eps: float = 1e-5, flops: int = 0) -> Op:
+    """x += W2 . gelu(W1 . LN(x) + b1) + b2 on the bf16 residual stream in one tcgen05 kernel, LayerNorm folded into
+    (w1f, u1, b1f) by fold_layernorm; optionally stats_out[row] = (rstd, -mean rstd) of the new rows
+    (include/cvb200.h cvb200_block_ffn)."""
+    _require_cuda(x, w1f, u1, b1f, w2, b2, out1, stats_out)
+    assert x.dtype == torch.bfloat16 and w1f.dtype == torch.bfloat16 and w2.dtype == torch.bfloat16
+    assert all(t.dtype == torch.float32 and t.is_contiguous() for t in (u1, b1f, b2))
+    assert tuple(w1f.shape) == (1024, 256) and tuple(w2.shape) == (256, 1024) and w1f.is_contiguous() and w2.is_contiguous()
+    assert out1 is None or out1.dtype == torch.bfloat16
+    assert stats_out is None or (stats_out.dtype == torch.float32 and stats_out.is_contiguous()
+                                 and stats_out.shape[0] >= lay.rows and stats_out.shape[-1] == 2)
+    lib = _lib.load()
+    layc = lay.c
+    args = (x.data_ptr(), x.stride(0), eps, w1f.data_ptr(), u1.data_ptr(), b1f.data_ptr(), w2.data_ptr(), b2.data_ptr(),
+            _ptr(out1), out1.stride(0) if out1 is not None else 0, _ptr(stats_out), C.byref(layc))
+    keep = (x, w1f, u1, b1f, w2, b2, out1, stats_out, lay, layc)
+
+    def launch(_keep=keep):
+        _lib.check(lib.cvb200_block_ffn(*args, _stream()), "block_ffn")
+    return _profiled("block_ffn", flops, launch)
 
 
 def layernorm_op(x, out, gamma, beta, rows: int, eps: float = 1e-5) -> Op:

@@ -134,6 +134,20 @@ def linear_plan(w: torch.Tensor, bias, dtype, device, c_pad: Optional[int] = Non
     return build_plan([[(0, 0, w)]], w.shape[0], c_pad or _pad64(w.shape[1]), bias, dtype, device)
 
 
+def folded_linear_plan(w: torch.Tensor, bias, gamma: torch.Tensor, beta: torch.Tensor, dtype, device) -> TapPlan:
+    """nn.Linear that consumes LayerNorm(x; gamma, beta), with the norm folded in (include/cvb200.h, epilogue.row_stats):
+    W . LN(x) + b = rstd (Wf . x) - rstd mean u + bf, Wf = W * gamma, u = rowsum of the ROUNDED Wf (the mean term then cancels
+    exactly), bf = b + W . beta.  The plan's A operand is the RAW x; plan.extra['row_u'] is u padded to n_pad."""
+    w = w.detach().float().reshape(w.shape[0], -1)
+    wf = w * gamma.detach().float().reshape(1, -1)
+    bf = w @ beta.detach().float().reshape(-1)
+    if bias is not None:
+        bf = bf + bias.detach().float().reshape(-1)
+    plan = build_plan([[(0, 0, wf)]], w.shape[0], _pad64(w.shape[1]), bf, dtype, device)
+    plan.extra["row_u"] = plan.W[0].float().sum(dim=1).contiguous()        # [n_pad] fp32, of the weights as rounded
+    return plan
+
+
 def conv1d_plan(w: torch.Tensor, bias, dtype, device, dilation: int = 1, pad_left: Optional[int] = None,
                 stride: int = 1, c_pad: Optional[int] = None, col_pitch: Optional[int] = None) -> TapPlan:
     """nn.Conv1d weight [N, C, k].  pad_left defaults to 'same' ((k-1)*dilation/2); a causal conv

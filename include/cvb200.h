@@ -57,6 +57,7 @@ extern "C" {
 #define CVB200_OUT1_LRELU 3
 
 /* Fused epilogue of the tap GEMM.  Per output element (row m, phase, column n):
+ *   acc = row_stats[m][0] * acc + row_stats[m][1] * row_u[n]   (only when row_stats != NULL: folded LayerNorm)
  *   v = acc + bias[n] + seq_bias[seq][n];  v = act(v);  v += res[m][phase*phase_col + n];
  *   v *= out_scale;  if (accumulate) v += out0[m][...];  rows beyond the valid length -> 0;
  *   out0[m][phase*phase_col + n] = v;  out1[...] = out1_fn(v);
@@ -86,6 +87,10 @@ typedef struct cvb200_epilogue {
   int32_t out1_dt;
   float out1_slope;
   int32_t gn_groups;
+  /* LayerNorm folded into the GEMM (A = the RAW rows, W = W * gamma): acc = row_stats[m][0] * acc + row_stats[m][1] * row_u[n]
+   * before the bias, with row_stats[m] = (rstd, -mean * rstd) of input row m, row_u[n] = sum_k W[n][k], bias = b + W . beta */
+  const float* row_stats;  /* [rows][2] or NULL */
+  const float* row_u;      /* [n_pad] */
 } cvb200_epilogue;
 
 /* The one contraction of the library ("tap GEMM"):
@@ -143,6 +148,20 @@ int cvb200_tapgemm(const cvb200_gemm* p, int engine, void* stream);
  * the new x.  Rows past a sequence's valid length are written as zeros.  The hidden activations stay in TMEM. */
 int cvb200_ffn_fused(const void* a, int lda, const void* w1, const float* b1, const void* w2, const float* b2, float* x,
                      int ldx, void* out1, int ldo1, const cvb200_layout* lay, void* stream);
+
+/* Second half of a BasicTransformerBlock on the bf16 residual stream, one kernel (csrc/block_ffn_tc.cu):
+ *   x += W2 . gelu(W1 . LayerNorm(x; g3, be3) + b1) + b2   (in place)
+ *        norm3 + ff + residual, cosyvoice/flow/components/transformer.py:300, :83-136, :309-314
+ *   stats_out[row] = (rstd, -mean * rstd) of the new row (optional): what norm1 of the NEXT block (:262) needs, consumed
+ *        by a tap GEMM through epilogue.row_stats
+ *   out1 = x_new (optional bf16 copy)
+ * The LayerNorm is folded into the first GEMM by the caller: w1f = bf16(W1 * g3[None, :]) [1024, 256],
+ * u1[j] = sum_k w1f[j, k] (fp32, of the ROUNDED weights), b1f = b1 + W1 . be3; then W1 . LN(x) + b1 = rstd (w1f . x) - rstd mean u1
+ * + b1f, with the row statistics computed inside the kernel.  x: bf16 [rows, ldx >= 256]; w2 bf16 [256, 1024]
+ * (nn.Linear layout); b2 [256] fp32.  Rows past a sequence's valid length are written as zeros (x, out1; stats 0, 0).
+ * The [rows, 1024] hidden activations never leave the SM (TMEM) and no normalised copy of x is written. */
+int cvb200_block_ffn(void* x, int ldx, float eps, const void* w1f, const float* u1, const float* b1f, const void* w2,
+                     const float* b2, void* out1, int ldo1, float* stats_out, const cvb200_layout* lay, void* stream);
 
 /* fp32 -> three bf16 operands with x = x1 + x2 + x3 (24 mantissa bits): out[row, i*cpad + c] = x_i[row, c], i = 0..2.
  * Lets the f0 predictor (cosyvoice/hifigan/f0_predictor.py:52-55, whose output is integrated into the source phase)

@@ -402,3 +402,85 @@ def test_ffn_fused_matches_torch(lens):
     ops.ffn_fused_op(a, w1, b1, w2, b2, x2, lay)()
     _sync()
     assert torch.equal(x2, x)
+
+
+@pytest.mark.parametrize("lens", [[200, 77], [128], [1000, 3, 640, 129], [609] * 40])
+def test_block_ffn_matches_torch(lens):
+    """cvb200_block_ffn (norm3 + FeedForward + residual in one tcgen05 kernel on the bf16 stream, LayerNorm folded into the
+    first GEMM, row statistics of the new stream as a side output) against torch:
+        x' = bf16(x + W2 . bf16(gelu(W1 . LN(x) + b1)) + b2),  stats = (rstd, -mean rstd) of x'.
+    Tolerances = bf16 rounding of the operands (K = 1024 reduction) and of the output.  The rows carry a common offset of
+    up to 3 sigma (the folded form must cancel the mean term).  The last case has more tiles than SMs (several tiles per CTA:
+    barrier phases, X-tile prefetch, TMEM reuse across tiles)."""
+    torch.manual_seed(41)
+    lay = SeqLayout.build(lens, DEV)
+    R = lay.rows
+    x0 = torch.zeros(R, 256, device=DEV)
+    for b, l in enumerate(lens):
+        x0[lay.row0[b]:lay.row0[b] + l] = torch.randn(l, 256, device=DEV) * 1.5 + 3 * torch.randn(l, 1, device=DEV)
+    x0 = x0.to(torch.bfloat16)
+    w1 = torch.randn(1024, 256, device=DEV) * (2.0 / 256) ** 0.5
+    w2 = (torch.randn(256, 1024, device=DEV) * (2.0 / 1024) ** 0.5).to(torch.bfloat16)
+    b1, b2 = torch.randn(1024, device=DEV) * 0.1, torch.randn(256, device=DEV) * 0.1
+    g3, be3 = 1 + 0.2 * torch.randn(256, device=DEV), 0.1 * torch.randn(256, device=DEV)
+    F = torch.nn.functional
+    w1f, u1, b1f = ops.fold_layernorm(w1, b1, g3, be3, torch.bfloat16)
+    # the folded operands reproduce the unfolded Linear(LayerNorm(x)) up to the bf16 rounding of W1 * gamma
+    a = F.layer_norm(x0.float(), (256,))
+    pre = a @ w1f.float().t() + b1f
+    pre_unfolded = F.layer_norm(x0.float(), (256,), g3, be3) @ w1.t() + b1
+    assert (pre - pre_unfolded).abs().max().item() < 0.05
+    h = F.gelu(pre).to(torch.bfloat16).float()
+    want_x = x0.float() + h @ w2.float().t() + b2
+    x = x0.clone()
+    out1 = torch.full((R, 256), 7.0, device=DEV, dtype=torch.bfloat16)
+    stats = torch.full((R, 2), 7.0, device=DEV)
+    ops.block_ffn_op(x, w1f, u1, b1f, w2, b2, lay, out1=out1, stats_out=stats)()
+    _sync()
+    mean = x.float().mean(dim=1)
+    rstd = torch.rsqrt(x.float().var(dim=1, unbiased=False) + 1e-5)
+    for b, l in enumerate(lens):
+        r0 = lay.row0[b]
+        got = x[r0:r0 + l].float()
+        scale = max(1.0, want_x[r0:r0 + l].abs().max().item())
+        err = (got - want_x[r0:r0 + l]).abs().max().item()
+        assert err < 2e-2 * scale, (b, l, err, scale)
+        assert torch.equal(out1[r0:r0 + l], x[r0:r0 + l])
+        assert torch.allclose(stats[r0:r0 + l, 0], rstd[r0:r0 + l], rtol=2e-4, atol=1e-6), (b, l)
+        assert torch.allclose(stats[r0:r0 + l, 1], -mean[r0:r0 + l] * rstd[r0:r0 + l], rtol=2e-4, atol=2e-4), (b, l)
+        for buf in (x, out1, stats):
+            assert buf[r0 + l:r0 + lay.strides[b]].float().abs().max().item() == 0
+    # without the optional outputs, and a second launch on the same buffers: identical stream
+    x2 = x0.clone()
+    ops.block_ffn_op(x2, w1f, u1, b1f, w2, b2, lay)()
+    _sync()
+    assert torch.equal(x2, x)
+
+
+def test_folded_layernorm_projection_matches_layernorm_then_projection():
+    """epilogue.row_stats: the QKV projection reading the RAW bf16 stream with norm1 folded into its weights (statistics
+    from cvb200_block_ffn's side output) against LayerNorm -> bf16 -> projection on the same engine, and against torch."""
+    from cosyvoice_b200.packing import folded_linear_plan, linear_plan
+    torch.manual_seed(43)
+    lens = [300, 77, 640]
+    lay = SeqLayout.build(lens, DEV)
+    R = lay.rows
+    x = torch.zeros(R, 256, device=DEV)
+    for b, l in enumerate(lens):
+        x[lay.row0[b]:lay.row0[b] + l] = torch.randn(l, 256, device=DEV) * 1.3 + 2 * torch.randn(l, 1, device=DEV)
+    x = x.to(torch.bfloat16)
+    w = torch.randn(1536, 256) * 0.06
+    g, be = 1 + 0.2 * torch.randn(256), 0.1 * torch.randn(256)
+    pf = folded_linear_plan(w, None, g, be, torch.bfloat16, DEV)
+    xf = x.float()
+    mean, rstd = xf.mean(dim=1), torch.rsqrt(xf.var(dim=1, unbiased=False) + 1e-5)
+    stats = torch.stack([rstd, -mean * rstd], dim=1).contiguous()
+    out = torch.zeros(R, 1536, device=DEV, dtype=torch.bfloat16)
+    ops.gemm_op(pf, x, lay, out, engine=_lib.ENGINE_TCGEN05, row_stats=stats, row_u=pf.extra["row_u"])()
+    _sync()
+    want = torch.nn.functional.layer_norm(xf, (256,), g.to(DEV), be.to(DEV)) @ w.to(DEV).t()
+    for b, l in enumerate(lens):
+        r0 = lay.row0[b]
+        err = (out[r0:r0 + l].float() - want[r0:r0 + l]).abs().max().item()
+        assert err < 3e-2 * max(1.0, want[r0:r0 + l].abs().max().item()), (b, err)
+        assert out[r0 + l:r0 + lay.strides[b]].float().abs().max().item() == 0
