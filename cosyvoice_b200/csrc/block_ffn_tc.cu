@@ -57,13 +57,22 @@ constexpr int BF_BK = 64;
 constexpr int BF_A_BYTES = BF_M * BF_C * 2;          // 64 KiB: 4 k-blocks of [128 x 64]
 constexpr int BF_STAGE_BYTES = 32 * 1024;            // G1: two [128 x 64] W1 boxes; G2: one [256 x 64] W2 box
 constexpr int BF_STAGES = 4;
-constexpr int BF_GELU_WARPS = 16;                    // warps 2..17
-constexpr int BF_ROW_WARPS = 4;                      // warps 18..21
+#ifndef BF_GELU_WARPS_N
+#define BF_GELU_WARPS_N 8
+#endif
+#ifndef BF_ROW_WARPS_N
+#define BF_ROW_WARPS_N 8
+#endif
+constexpr int BF_GELU_WARPS = BF_GELU_WARPS_N;        // 8 or 16: a thread owns 64 or 32 hidden units of a chunk
+constexpr int BF_ROW_WARPS = BF_ROW_WARPS_N;          // 4 or 8: a thread owns a whole row or half of it
+constexpr int BF_GELU_COLS = 128 / (BF_GELU_WARPS / 4);
+constexpr int BF_ROW_SPLIT = BF_ROW_WARPS / 4;
+constexpr int BF_ROW_COLS = 256 / BF_ROW_SPLIT;
 constexpr int BF_THREADS = 32 * (2 + BF_GELU_WARPS + BF_ROW_WARPS);
 constexpr int BF_TM_H = 0, BF_TM_O = 256, BF_TM_COLS = 512;
 constexpr int BF_BAR_BYTES = 256;
 constexpr int BF_VEC_FLOATS = 2 * BF_H + BF_C;       // b1' | u | b2
-constexpr int BF_XCH_BYTES = 2 * BF_M * 8;           // row statistics [tile parity][row] float2 (rstd, -mean rstd)
+constexpr int BF_XCH_BYTES = 2 * BF_M * 8 + 2 * 2 * BF_M * 8;   // row statistics [tile parity][row] float2 + half-row exchange [use parity][half][row]
 constexpr int BF_SMEM = 1024 + BF_A_BYTES + BF_STAGES * BF_STAGE_BYTES + BF_BAR_BYTES + BF_VEC_FLOATS * 4 + BF_XCH_BYTES;
 
 #ifdef BF_PROFILE
@@ -146,6 +155,7 @@ block_ffn_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
   float* su1 = sb1 + BF_H;
   float* sb2 = su1 + BF_H;
   float2* srow = reinterpret_cast<float2*>(sb2 + BF_C);          // [2][128] (rstd, -mean rstd) of the tile's rows
+  float2* xch = srow + 2 * BF_M;                                 // [2][2][128] partial statistics of half rows
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   if (threadIdx.x == 0) {
@@ -298,7 +308,7 @@ block_ffn_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
   } else if (warp < 2 + BF_GELU_WARPS) {
     // ------------------------------------------------------------------ GELU warps
     const int q = warp & 3;                    // TMEM lane quadrant this warp may access
-    const int sub = (warp - 2) >> 2;           // 32-column slice of an H chunk
+    const int sub = (warp - 2) >> 2;           // this thread's BF_GELU_COLS-column slice of an H chunk
     const uint32_t tbase = tmem + ((uint32_t)(q * 32) << 16);
     const uint32_t sb1_addr = ptx::smem_u32(sb1), su1_addr = ptx::smem_u32(su1);
     const int trow = q * 32 + lane;
@@ -313,25 +323,31 @@ block_ffn_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
         BF_WAIT(prof[7], &h_full[hb], hcount[hb] & 1);
         ++hcount[hb];
         ptx::tc_fence_after();
-        const uint32_t haddr = tbase + BF_TM_H + hb * BF_CH + sub * 32;
-        uint32_t r[32];
-        ptx::tmem_ld32_nowait(haddr, r);
-        ptx::tmem_wait_ld();
-        uint32_t pk[16];                       // the slice's 32 units go back packed into its first 16 columns
 #pragma unroll
-        for (int i = 0; i < 32; i += 4) {
-          float bb[4], uu[4];
-          const uint32_t off = (c * BF_CH + sub * 32 + i) * 4;
-          lds128f(sb1_addr + off, bb);
-          lds128f(su1_addr + off, uu);
-          const float2 x0 = __ffma2_rn(make_float2(__uint_as_float(r[i]), __uint_as_float(r[i + 1])), rs,
-                                       __ffma2_rn(rb, make_float2(uu[0], uu[1]), make_float2(bb[0], bb[1])));
-          const float2 x1 = __ffma2_rn(make_float2(__uint_as_float(r[i + 2]), __uint_as_float(r[i + 3])), rs,
-                                       __ffma2_rn(rb, make_float2(uu[2], uu[3]), make_float2(bb[2], bb[3])));
-          pk[i >> 1] = gelu_pair_bf16(x0);
-          pk[(i >> 1) + 1] = gelu_pair_bf16(x1);
+        for (int s2 = 0; s2 < BF_GELU_COLS / 32; ++s2) {
+          // one 32-column slice at a time (its 32 units go back packed into its first 16 columns): only 32 raw values are
+          // live, which leaves the registers the compiler needs to keep several GELU chains in flight
+          const int col = sub * BF_GELU_COLS + s2 * 32;
+          const uint32_t haddr = tbase + BF_TM_H + hb * BF_CH + col;
+          uint32_t r[32];
+          ptx::tmem_ld32_nowait(haddr, r);
+          ptx::tmem_wait_ld();
+          uint32_t pk[16];
+#pragma unroll
+          for (int i = 0; i < 32; i += 4) {
+            float bb[4], uu[4];
+            const uint32_t off = (c * BF_CH + col + i) * 4;
+            lds128f(sb1_addr + off, bb);
+            lds128f(su1_addr + off, uu);
+            const float2 x0 = __ffma2_rn(make_float2(__uint_as_float(r[i]), __uint_as_float(r[i + 1])), rs,
+                                         __ffma2_rn(rb, make_float2(uu[0], uu[1]), make_float2(bb[0], bb[1])));
+            const float2 x1 = __ffma2_rn(make_float2(__uint_as_float(r[i + 2]), __uint_as_float(r[i + 3])), rs,
+                                         __ffma2_rn(rb, make_float2(uu[2], uu[3]), make_float2(bb[2], bb[3])));
+            pk[i >> 1] = gelu_pair_bf16(x0);
+            pk[(i >> 1) + 1] = gelu_pair_bf16(x1);
+          }
+          ptx::tmem_st16(haddr, pk);
         }
-        ptx::tmem_st16(haddr, pk);
         ptx::tmem_wait_st();
         ptx::tc_fence_before();
         __syncwarp();
@@ -340,21 +356,37 @@ block_ffn_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
     }
   } else {
     // ------------------------------------------------------------------ row warps: row statistics + drain
-    // thread = one whole row of the tile (its TMEM lane): no cross-thread exchange anywhere
+    // thread = row trow (its TMEM lane) x BF_ROW_COLS columns.  With eight row warps the two halves of a row live in the two
+    // warps of a lane quadrant and merge their partial statistics through smem (named barrier per quadrant, 64 threads).
     const int q = warp & 3;
+    const int hf = (warp - 2 - BF_GELU_WARPS) >> 2;                          // 0 .. BF_ROW_SPLIT-1
     const int trow = q * 32 + lane;
+    const int c0 = hf * BF_ROW_COLS;                                         // first column of this thread's part
     const uint32_t tbase = tmem + ((uint32_t)(q * 32) << 16);
-    const uint32_t a_row = ptx::smem_u32(sA) + trow * 128;
+    const uint32_t a_row = ptx::smem_u32(sA) + (c0 / 64) * 16384 + trow * 128;
     const int swz = trow & 7;
-    const uint32_t sb2_addr = ptx::smem_u32(sb2);
+    const uint32_t sb2_addr = ptx::smem_u32(sb2) + c0 * 4;
+    int xuse = 0;
 
-    // (pivot, sum of (x - pivot), sum of (x - pivot)^2) over 256 values -> (rstd, -mean rstd); the shift by the first value
-    // removes the cancellation of a common offset
+    // (pivot, sum of (x - pivot), sum of (x - pivot)^2) over this thread's columns -> (rstd, -mean rstd) of the whole row.
+    // The shift by the first value removes the cancellation of a common offset; halves are merged with Chan's formula.
     auto finish = [&](float pivot, float2 s, float2 ss) {
-      const float md = (s.x + s.y) * (1.f / 256.f);
-      const float var = fmaxf((ss.x + ss.y) * (1.f / 256.f) - md * md, 0.f);
-      const float rstd = rsqrtf(var + eps);
-      return make_float2(rstd, -(pivot + md) * rstd);
+      constexpr float inv_n = 1.f / BF_ROW_COLS;
+      const float sd = s.x + s.y;
+      float mean = pivot + sd * inv_n;
+      float m2 = fmaxf((ss.x + ss.y) - sd * sd * inv_n, 0.f);
+      if (BF_ROW_SPLIT == 2) {
+        float2* xp = xch + (xuse & 1) * 2 * BF_M;
+        ++xuse;
+        xp[hf * BF_M + trow] = make_float2(mean, m2);
+        ptx::named_bar_sync(1 + q, 64);
+        const float2 o = xp[(hf ^ 1) * BF_M + trow];
+        const float d = mean - o.x;
+        m2 = m2 + o.y + (0.5f * BF_ROW_COLS) * d * d;
+        mean = 0.5f * (mean + o.x);
+      }
+      const float rstd = rsqrtf(m2 * (1.f / 256.f) + eps);
+      return make_float2(rstd, -mean * rstd);
     };
 
     // norm3 statistics of row trow of the X tile (read-only pass over the swizzled smem tile)
@@ -364,7 +396,7 @@ block_ffn_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
       float2 s = f2(0.f), ss = f2(0.f);
       float pivot = 0.f;
 #pragma unroll
-      for (int kb = 0; kb < 4; ++kb) {
+      for (int kb = 0; kb < BF_ROW_COLS / 64; ++kb) {
         uint32_t r[8][4];
 #pragma unroll
         for (int j = 0; j < 8; ++j) lds128(a_row + kb * 16384 + ((j ^ swz) << 4), r[j]);
@@ -379,7 +411,8 @@ block_ffn_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
           }
         }
       }
-      srow[(n & 1) * BF_M + trow] = finish(pivot, s, ss);
+      const float2 st = finish(pivot, s, ss);
+      if (hf == 0) srow[(n & 1) * BF_M + trow] = st;
       __syncwarp();
       if (lane == 0) ptx::mbar_arrive(st_full);
       BF_T1(prof[6]);
@@ -396,18 +429,19 @@ block_ffn_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
                    : "memory");
     };
 
+    constexpr int NG = BF_ROW_COLS / 32;       // 32-column groups per thread
     int n = 0;
     stats_tile(0);
     for (int t = t_first; t < m_tiles; t += t_step, ++n) {
       // ---- the next tile's row statistics first: the GELU warps need them at its chunk 0
       if (t + t_step < m_tiles) stats_tile(n + 1);
 
-      // ---- drain: O + b2 + X -> X (bf16), the row in eight 32-column groups; the residual (L2-resident: the TMA read it
-      // a tile ago) is requested two groups ahead, the first two before the wait on the last GEMM
+      // ---- drain: O + b2 + X -> X (bf16) in 32-column groups; the residual (L2-resident: the TMA read it a tile ago) is
+      // requested two groups ahead, the first two before the wait on the last GEMM
       const int row = t * BF_M + trow;
       const int b = __ldg(lay.tile_seq + t);
       const bool valid = __ldg(lay.tile_row0 + t) + trow < __ldg(lay.seq_len + b);
-      __nv_bfloat16* xr = X + (size_t)row * ldx;
+      __nv_bfloat16* xr = X + (size_t)row * ldx + c0;
       uint32_t res[2][2][8];                   // [group parity][16-column half][8 packed pairs]
 #pragma unroll
       for (int k = 0; k < 2; ++k) {
@@ -422,10 +456,10 @@ block_ffn_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
       float2 s = f2(0.f), ss = f2(0.f);
       float pivot = 0.f;
 #pragma unroll
-      for (int k = 0; k < 8; ++k) {
+      for (int k = 0; k < NG; ++k) {
         float v[32];
-        ptx::tmem_ld32(tbase + BF_TM_O + k * 32, v);
-        if (k == 7) {                          // the whole row of O is in registers: the next tile's G2 may overwrite it
+        ptx::tmem_ld32(tbase + BF_TM_O + c0 + k * 32, v);
+        if (k == NG - 1) {                     // this thread's part of O is in registers: the next tile's G2 may overwrite it
           ptx::tc_fence_before();
           __syncwarp();
           if (lane == 0) ptx::mbar_arrive(o_free);
@@ -454,21 +488,24 @@ block_ffn_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
             }
           }
           stg256(xr + k * 32 + g16 * 16, y);
-          if (out1) stg256(out1 + (size_t)row * ldo1 + k * 32 + g16 * 16, y);
+          if (out1) stg256(out1 + (size_t)row * ldo1 + c0 + k * 32 + g16 * 16, y);
         }
-        if (k < 6) {
+        if (k + 2 < NG) {
           ldg256(xr + (k + 2) * 32, res[k & 1][0]);
           ldg256(xr + (k + 2) * 32 + 16, res[k & 1][1]);
         }
       }
-      if (stats_out) stats_out[row] = valid ? finish(pivot, s, ss) : make_float2(0.f, 0.f);
+      if (stats_out) {
+        const float2 st = finish(pivot, s, ss);
+        if (hf == 0) stats_out[row] = valid ? st : make_float2(0.f, 0.f);
+      }
 #ifdef BF_PROFILE
       prof[9] += clock64() - _td;
 #endif
     }
   }
 #ifdef BF_PROFILE
-  if (blockIdx.x == 0 && lane == 0 && (warp == 1 || warp == 2 || warp == 18))
+  if (blockIdx.x == 0 && lane == 0 && (warp == 1 || warp == 2 || warp == 2 + BF_GELU_WARPS))
     printf("block_ffn prof warp %d total %lld | mma: a_full %lld p_full %lld o_free %lld g2 w_full %lld g1 w_full %lld | "
            "row: a_full %lld stats %lld | gelu: h_full %lld st_full %lld | row: o_full %lld drain %lld\n", warp, clock64() - t_start,
            prof[0], prof[1], prof[2], prof[3], prof[4], prof[5], prof[6], prof[7], prof[10], prof[8], prof[9]);

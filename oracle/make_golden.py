@@ -129,6 +129,47 @@ def act1d():
                            down_filter=m.downsample.lowpass.filter.reshape(-1).clone()))
 
 
+def _bigvgan_trunk(m, feat, spk):
+    """bigvgan.py:406-436 driven through the REAL module's own layers (the encoders in front of the trunk are out of scope)."""
+    with torch.no_grad():
+        x = m.conv_pre(feat)
+        x = x + m.cond_layer(spk)
+        for i in range(m.num_upsamples):
+            x = m.ups[i][0](x)
+            x = x + m.conds[i](spk)
+            xs = None
+            for j in range(m.num_kernels):
+                r = m.resblocks[i * m.num_kernels + j](x)
+                xs = r if xs is None else xs + r
+            x = xs / m.num_kernels
+        x = m.activation_post(x)
+        x = m.conv_post(x)
+        return torch.tanh(x).squeeze(1)
+
+
+def _bigvgan_module(topology, seed):
+    m = R.build_bigvgan(topology).eval()
+    res = m.load_state_dict(W.bigvgan_sd(topology, seed=seed), strict=False)
+    assert not res.unexpected_keys, res.unexpected_keys
+    allowed = ("input_embedding.", "encoder_proj.", "mel_proj.")
+    bad = [k for k in res.missing_keys if not k.startswith(allowed) and not k.endswith(".filter")]
+    assert not bad, bad
+    return m
+
+
+def bigvgan_config4(members=(0, 31, 63), B=64, frames=94):
+    """BASELINE config 4 at its own size: the 24 kHz / 100-band trunk on a batch of 64 mels of 94 frames (1 s), inputs
+    N(0,1)*2-4 and speaker vectors N(0,1) from torch.Generator seed 5 exactly as tools/bench_configs.py `bigvgan` draws them.
+    The REAL reference runs three members one by one (B = 1, as the reference would); only their waveforms are stored, the
+    tests regenerate the inputs from the seed."""
+    m = _bigvgan_module("24k100", 3)
+    g = torch.Generator().manual_seed(5)
+    feat = torch.randn(B, 100, frames, generator=g) * 2 - 4
+    spk = torch.randn(B, 512, 1, generator=g)
+    wavs = {int(i): _bigvgan_trunk(m, feat[i:i + 1], spk[i:i + 1])[0].contiguous() for i in members}
+    _save("bigvgan_config4.pt", dict(weights_seed=3, topology="24k100", input_seed=5, batch=B, frames=frames, wavs=wavs))
+
+
 def bigvgan(topology="24k100"):
     m = R.build_bigvgan(topology).eval()
     sd = W.bigvgan_sd(topology, seed=2)
@@ -142,20 +183,7 @@ def bigvgan(topology="24k100"):
     in_ch = 100 if topology == "24k100" else 1024
     feat = torch.randn(B, in_ch, T, generator=g)
     spk = torch.randn(B, 512, 1, generator=g)
-    with torch.no_grad():      # bigvgan.py:406-436 driven through the module's own layers
-        x = m.conv_pre(feat)
-        x = x + m.cond_layer(spk)
-        for i in range(m.num_upsamples):
-            x = m.ups[i][0](x)
-            x = x + m.conds[i](spk)
-            xs = None
-            for j in range(m.num_kernels):
-                r = m.resblocks[i * m.num_kernels + j](x)
-                xs = r if xs is None else xs + r
-            x = xs / m.num_kernels
-        x = m.activation_post(x)
-        x = m.conv_post(x)
-        wav = torch.tanh(x).squeeze(1)
+    wav = _bigvgan_trunk(m, feat, spk)
     _save(f"bigvgan_{topology}.pt", dict(weights_seed=2, topology=topology, feat=feat, spk=spk, wav=wav))
 
 
@@ -285,6 +313,8 @@ if __name__ == "__main__":
     hift(True)
     act1d()
     bigvgan("24k100")
+    bigvgan("fork")
+    bigvgan_config4()
     token2wav()
     frontend(False)
     frontend(True)
