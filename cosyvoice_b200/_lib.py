@@ -16,7 +16,7 @@ MAX_SEGS = 32
 ACT_NONE, ACT_GELU, ACT_ELU, ACT_SNAKE, ACT_LRELU, ACT_MISH, ACT_TANH, ACT_SILU = range(8)
 RES_NONE, RES_F32, RES_ACT = range(3)
 OUT1_NONE, OUT1_COPY, OUT1_SNAKE, OUT1_LRELU = range(4)
-ATTN_TCGEN05, ATTN_MMA_SYNC = 0, 1
+ATTN_TCGEN05, ATTN_MMA_SYNC, ATTN_TCGEN05_V2 = 0, 1, 2
 
 
 class Epilogue(C.Structure):

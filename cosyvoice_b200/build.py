@@ -12,7 +12,7 @@ CSRC = os.path.join(HERE, "csrc")
 LIB_DIR = os.path.join(HERE, "lib")
 OBJ_DIR = os.path.join(HERE, "build")
 LIB = os.path.join(LIB_DIR, "libcvb200.so")
-SOURCES = ["api.cu", "glue.cu", "attention.cu", "attention_tc.cu", "vocoder.cu", "antialias.cu", "tapgemm_simt.cu", "tapgemm_tc.cu", "ffn_tc.cu", "block_ffn_tc.cu", "encoder.cu"]
+SOURCES = ["api.cu", "glue.cu", "attention.cu", "attention_tc.cu", "attention_tc2.cu", "vocoder.cu", "antialias.cu", "tapgemm_simt.cu", "tapgemm_tc.cu", "ffn_tc.cu", "block_ffn_tc.cu", "encoder.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC", "--expt-relaxed-constexpr"]
 

@@ -39,6 +39,7 @@ int launch_nct_to_rows(const float*, long long, long long, int, void*, int, int,
 int launch_rows_to_nct(const float*, int, int, float*, long long, long long, const Layout&, cudaStream_t);
 int launch_attention(const void*, int, void*, int, int, const Layout&, int, float, cudaStream_t);
 int launch_attention_tc(const void*, int, void*, int, const Layout&, int, float, cudaStream_t);
+int launch_attention_tc2(const void*, int, void*, int, const Layout&, int, float, cudaStream_t);
 int launch_rowdot_abs(const void*, int, int, const float*, const float*, int, float*, int, cudaStream_t);
 int launch_sine_source(const float*, const Layout&, int, float, const float*, const float*, const float*, const float*,
                        double*, float*, long long, cudaStream_t);
@@ -159,12 +160,14 @@ int cvb200_attention_ex(const void* qkv, int ld, void* out, int ldo, int dt, con
   NEED(qkv, "qkv"); NEED(out, "out"); NEED(lay, "layout");
   if (dt == CVB200_BF16 && impl == CVB200_ATTN_TCGEN05)
     return launch_attention_tc(qkv, ld, out, ldo, *lay, heads, scale, ST(stream));
+  if (dt == CVB200_BF16 && impl == CVB200_ATTN_TCGEN05_V2)
+    return launch_attention_tc2(qkv, ld, out, ldo, *lay, heads, scale, ST(stream));
   return launch_attention(qkv, ld, out, ldo, dt, *lay, heads, scale, ST(stream));
 }
 
 int cvb200_attention(const void* qkv, int ld, void* out, int ldo, int dt, const cvb200_layout* lay, int heads,
                      float scale, void* stream) {
-  return cvb200_attention_ex(qkv, ld, out, ldo, dt, lay, heads, scale, CVB200_ATTN_TCGEN05, stream);
+  return cvb200_attention_ex(qkv, ld, out, ldo, dt, lay, heads, scale, CVB200_ATTN_TCGEN05_V2, stream);
 }
 
 int cvb200_time_sinusoid(const float* t, int S, int dim, float scale, float* out, void* stream) {

@@ -245,41 +245,49 @@ block_ffn_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
     }
   } else if (warp == 1) {
     // ------------------------------------------------------------------ MMA issuer
-    if (lane == 0) {
+    // whole warp, uniform state, one elected lane issues (ptx.cuh "lean issue path": with the loop inside `if (lane == 0)`
+    // every UTCHMMA carried a ~20-instruction uniform-register conversion loop and G1's 64-cycle MMAs were issue-bound)
+    {
       const uint32_t idesc1 = ptx::make_idesc_bf16(BF_M, BF_CH);       // 128 x 128
       const uint32_t idesc2 = ptx::make_idesc_bf16(BF_M, BF_C);        // 128 x 256
-      const uint32_t a_base = ptx::smem_u32(sA);
+      const uint32_t desc_hi = (uint32_t)(ptx::make_sw128_kmajor_desc(0) >> 32);
+      const uint32_t a_lo0 = (uint32_t)ptx::make_sw128_kmajor_desc(ptx::smem_u32(sA));
+      const uint32_t w_lo0 = (uint32_t)ptx::make_sw128_kmajor_desc(ptx::smem_u32(sW));
       int stage = 0;
       uint32_t ph = 0;
       auto next_stage = [&]() { if (++stage == BF_STAGES) { stage = 0; ph ^= 1; } };
       uint32_t hcount[2] = {0, 0};           // completed uses of each H buffer (for the p_full parity)
-      auto issue_g1 = [&](int c) {
+      auto issue_g1 = [&](int c, bool free_a) {
         const uint32_t d = tmem + BF_TM_H + (c & 1) * BF_CH;
         for (int h = 0; h < 2; ++h) {
           BF_WAIT(prof[4], &w_full[stage], ph);
           ptx::tc_fence_after();
-          const uint32_t w_base = ptx::smem_u32(sW + stage * BF_STAGE_BYTES);
+          const uint32_t w_lo = ptx::bcast0(w_lo0 + stage * (BF_STAGE_BYTES >> 4));
+          const uint32_t a_lo = ptx::bcast0(a_lo0 + 2 * h * (16384 >> 4));
+          const uint32_t hu = ptx::bcast0(h), fa = ptx::bcast0(free_a);
+          if (ptx::elect_one()) {
 #pragma unroll
-          for (int kk = 0; kk < 8; ++kk) {       // 2 k-blocks x 4 K16 steps
-            const int kb = 2 * h + (kk >> 2), k = kk & 3;
-            ptx::umma_ss(d, ptx::make_sw128_kmajor_desc(a_base + kb * 16384 + k * 32),
-                         ptx::make_sw128_kmajor_desc(w_base + (kk >> 2) * 16384 + k * 32), idesc1, (h | kk) != 0);
+            for (int kk = 0; kk < 8; ++kk) {       // 2 k-blocks x 4 K16 steps
+              const uint32_t off = (kk >> 2) * (16384 >> 4) + (kk & 3) * 2;
+              ptx::umma_ss_lo(d, a_lo + off, desc_hi, w_lo + off, desc_hi, idesc1, kk == 0 ? hu : 1u);
+            }
+            ptx::umma_commit(&w_empty[stage]);
+            if (hu) {
+              ptx::umma_commit(&h_full[c & 1]);
+              if (fa) ptx::umma_commit(a_free);    // all G1 of this tile are issued: A is free when they retire
+            }
           }
-          ptx::umma_commit(&w_empty[stage]);
+          __syncwarp();
           next_stage();
         }
-        ptx::umma_commit(&h_full[c & 1]);
       };
       int n = 0;
       for (int t = t_first; t < m_tiles; t += t_step, ++n) {
         BF_WAIT(prof[0], a_full, n & 1);          // the raw tile is the operand: nothing sits between the load and G1(0)
         ptx::tc_fence_after();
-        issue_g1(0);
+        issue_g1(0, false);
         for (int c = 0; c < BF_NCH; ++c) {
-          if (c + 1 < BF_NCH) {
-            issue_g1(c + 1);
-            if (c + 2 == BF_NCH) ptx::umma_commit(a_free);       // all G1 of this tile are issued: A is free when they retire
-          }
+          if (c + 1 < BF_NCH) issue_g1(c + 1, c + 2 == BF_NCH);
           const int hb = c & 1;
           BF_WAIT(prof[1], &p_full[hb], hcount[hb] & 1);
           ++hcount[hb];
@@ -289,20 +297,23 @@ block_ffn_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
           for (int j = 0; j < 2; ++j) {
             BF_WAIT(prof[3], &w_full[stage], ph);
             ptx::tc_fence_after();
-            const uint32_t w_base = ptx::smem_u32(sW + stage * BF_STAGE_BYTES);
+            const uint32_t w_lo = ptx::bcast0(w_lo0 + stage * (BF_STAGE_BYTES >> 4));
+            const uint32_t cj = ptx::bcast0((c | j) != 0), last = ptx::bcast0(c + 1 == BF_NCH && j == 1);
+            const uint32_t hj = ptx::bcast0(hbase + 64 * j);
+            if (ptx::elect_one()) {
 #pragma unroll
-            for (int k = 0; k < 4; ++k) {
-              // K16 step u = 4j + k of the chunk: hidden units [16u, 16u+16) live in packed columns
-              // 32*(u/2) + 8*(u%2) (the 32 units of a 32-column slice are packed into its first 16 columns)
-              const int u = 4 * j + k;
-              ptx::umma_ts(tmem + BF_TM_O, hbase + 32 * (u >> 1) + 8 * (u & 1),
-                           ptx::make_sw128_kmajor_desc(w_base + k * 32), idesc2, (c | u) != 0);
+              for (int k = 0; k < 4; ++k) {
+                // K16 step u = 4j + k of the chunk: hidden units [16u, 16u+16) live in packed columns
+                // 32*(u/2) + 8*(u%2) (the 32 units of a 32-column slice are packed into its first 16 columns)
+                ptx::umma_ts_lo(tmem + BF_TM_O, hj + 32 * (k >> 1) + 8 * (k & 1), w_lo + k * 2, desc_hi, idesc2, k == 0 ? cj : 1u);
+              }
+              ptx::umma_commit(&w_empty[stage]);
+              if (last) ptx::umma_commit(o_full);
             }
-            ptx::umma_commit(&w_empty[stage]);
+            __syncwarp();
             next_stage();
           }
         }
-        ptx::umma_commit(o_full);
       }
     }
   } else if (warp < 2 + BF_GELU_WARPS) {

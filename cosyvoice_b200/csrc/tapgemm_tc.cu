@@ -144,9 +144,14 @@ tapgemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     }
   } else if (warp == 1) {
     // ------------------------------------------------------------------ MMA issuer
-    if (lane == 0) {
+    // whole warp, uniform state, one elected lane issues (ptx.cuh "lean issue path")
+    {
       const uint32_t idesc = ptx::make_idesc_bf16(TILE_M, bn);
       const int kblocks = p.n_seg * chunks_per_seg;
+      const uint32_t desc_hi = (uint32_t)(ptx::make_sw128_kmajor_desc(0) >> 32);
+      const uint32_t a_lo0 = (uint32_t)ptx::make_sw128_kmajor_desc(ptx::smem_u32(sA));
+      const uint32_t b_lo0 = (uint32_t)ptx::make_sw128_kmajor_desc(ptx::smem_u32(sB));
+      const uint32_t b_step = (resident ? bn * GEMM_BK * 2 : B_STAGE_BYTES) >> 4;
       int stage = 0;
       uint32_t ph = 0;
       int acc = 0;
@@ -159,17 +164,19 @@ tapgemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
         for (int kb = 0; kb < kblocks; ++kb) {
           ptx::mbar_wait(&full[stage], ph);
           ptx::tc_fence_after();
-          const uint32_t a_base = ptx::smem_u32(sA + stage * A_STAGE_BYTES);
-          const uint32_t b_base = ptx::smem_u32(resident ? sB + kb * (bn * GEMM_BK * 2) : sB + stage * B_STAGE_BYTES);
+          const uint32_t a_lo = ptx::bcast0(a_lo0 + stage * (A_STAGE_BYTES >> 4));
+          const uint32_t b_lo = ptx::bcast0(b_lo0 + (resident ? kb : stage) * b_step);
+          const uint32_t first = ptx::bcast0(kb != 0);
+          if (ptx::elect_one()) {
 #pragma unroll
-          for (int k = 0; k < GEMM_BK / 16; ++k) {
-            ptx::umma_ss(d_tmem, ptx::make_sw128_kmajor_desc(a_base + k * 32), ptx::make_sw128_kmajor_desc(b_base + k * 32),
-                         idesc, (kb | k) != 0);
+            for (int k = 0; k < GEMM_BK / 16; ++k)
+              ptx::umma_ss_lo(d_tmem, a_lo + k * 2, desc_hi, b_lo + k * 2, desc_hi, idesc, k == 0 ? first : 1u);
+            ptx::umma_commit(&empty[stage]);      // frees the smem slot when these MMAs retire
+            if (kb + 1 == kblocks) ptx::umma_commit(&tfull[acc]);   // accumulator complete -> epilogue
           }
-          ptx::umma_commit(&empty[stage]);      // frees the smem slot when these MMAs retire
+          __syncwarp();
           if (++stage == STAGES) { stage = 0; ph ^= 1; }
         }
-        ptx::umma_commit(&tfull[acc]);          // accumulator complete -> epilogue
         acc ^= 1;
         if (acc == 0) acc_ph ^= 1;
       }

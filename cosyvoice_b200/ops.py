@@ -249,7 +249,7 @@ def norm_mish_op(h, out, gamma, beta, lay: SeqLayout, gn_stats=None, seq_bias=No
 
 
 def attention_op(qkv, out, lay: SeqLayout, heads: int, scale: float, flops: int = 0,
-                 impl: int = _lib.ATTN_TCGEN05) -> Op:
+                 impl: int = _lib.ATTN_TCGEN05_V2) -> Op:
     _require_cuda(qkv, out)
     lib = _lib.load()
     assert qkv.dtype == out.dtype

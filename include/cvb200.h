@@ -207,10 +207,12 @@ int cvb200_norm_mish(const void* h, int ldh, int h_dt, void* out, int ldo, int o
  * additive mask of flow/decoder.py:258). */
 int cvb200_attention(const void* qkv, int ld, void* out, int ldo, int dt, const cvb200_layout* lay,
                      int heads, float scale, void* stream);
-/* same, with an explicit kernel choice for bf16: 0 = tcgen05/TMEM flash kernel (default of cvb200_attention),
- * 1 = warp-level mma.sync flash kernel (kept as the on-device cross-check) */
+/* same, with an explicit kernel choice for bf16: 0 = first tcgen05/TMEM flash kernel (two CTAs per SM, two threads per
+ * query row), 1 = warp-level mma.sync flash kernel (kept as the on-device cross-check), 2 = second tcgen05/TMEM kernel
+ * (one CTA per SM running two independent work streams, one softmax thread per query row; default of cvb200_attention) */
 #define CVB200_ATTN_TCGEN05 0
 #define CVB200_ATTN_MMA_SYNC 1
+#define CVB200_ATTN_TCGEN05_V2 2
 int cvb200_attention_ex(const void* qkv, int ld, void* out, int ldo, int dt, const cvb200_layout* lay,
                         int heads, float scale, int impl, void* stream);
 

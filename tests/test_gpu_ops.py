@@ -200,7 +200,10 @@ def test_layernorm_and_norm_mish(dtype):
 
 @pytest.mark.parametrize("dtype,lens,impl", [(torch.float32, [70, 200], 0),
                                              (torch.bfloat16, [70, 200, 1, 64, 128, 650], _lib.ATTN_MMA_SYNC),
-                                             (torch.bfloat16, [70, 200, 1, 64, 128, 650, 129, 1218], _lib.ATTN_TCGEN05)])
+                                             (torch.bfloat16, [70, 200, 1, 64, 128, 650, 129, 1218], _lib.ATTN_TCGEN05),
+                                             (torch.bfloat16, [70, 200, 1, 64, 128, 650, 129, 1218], _lib.ATTN_TCGEN05_V2),
+                                             (torch.bfloat16, [609] * 64, _lib.ATTN_TCGEN05_V2),
+                                             (torch.bfloat16, [300], _lib.ATTN_TCGEN05_V2)])
 def test_attention(dtype, lens, impl):
     torch.manual_seed(5)
     lay = SeqLayout.build(lens, DEV)
