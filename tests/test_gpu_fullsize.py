@@ -174,3 +174,115 @@ def test_stft_istft_identity_and_unmasked_chunk_at_full_length():
         ops.relpos_attention_op(qkv, P, 511, u, u, o, la, 8, 0.125, chunk)()
         outs.append(o)
     assert torch.equal(outs[0], outs[1]) and torch.equal(outs[0], outs[2])
+
+
+# ----------------------------------------------------------------------------------------------- config 4 (BigVGAN) at its size
+def _snr_db(x, ref):
+    return (10 * torch.log10(ref.pow(2).mean() / (x - ref).pow(2).mean().clamp_min(1e-30))).item()
+
+
+def test_config4_bigvgan_batch64_of_94_frames_matches_the_reference_recordings():
+    """BASELINE config 4 at its own size: the 24 kHz / 100-band BigVGAN trunk on 64 mels of 94 frames (1 s each), inputs
+    drawn exactly as tools/bench_configs.py `bigvgan` draws them (torch.Generator seed 5).  Three members were run one by
+    one through the REAL reference trunk (oracle/make_golden.py bigvgan_config4 -> tests/golden/bigvgan_config4.pt):
+    fp32 engine max-abs < 2e-4 against them (the small-case bar); a permuted batch returns bit-identical permuted waveforms;
+    the bf16 (tcgen05) trunk keeps an SNR > 30 dB (and max-abs < 0.1 on the +-1 tanh output) against the reference's fp32
+    waveform.  The reference never runs this vocoder in half precision, so the bound is ours, stated as a signal-to-noise
+    ratio: bf16 operands (2^-9 relative rounding, fp32 accumulation) through the trunk's ~75 convolutions measure 36 dB."""
+    from cosyvoice_b200.bigvgan import B200BigVGAN
+    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "bigvgan_config4.pt")
+    d = torch.load(path, weights_only=True)
+    B, frames = d["batch"], d["frames"]
+    g = torch.Generator().manual_seed(d["input_seed"])
+    feat = torch.randn(B, 100, frames, generator=g) * 2 - 4
+    spk = torch.randn(B, 512, 1, generator=g)
+    sd = init_weights.bigvgan_sd(d["topology"], seed=d["weights_seed"])
+    g32 = B200BigVGAN(sd, d["topology"], dtype=torch.float32, device=DEV)
+    wav32 = g32.inference(feat, spk).cpu()
+    assert wav32.shape == (B, frames * 256)
+    for i, want in d["wavs"].items():
+        err = (wav32[i] - want).abs().max().item()
+        print(f"config 4 fp32 member {i}: max-abs {err:.3e}")
+        assert err < 2e-4, (i, err)
+    del g32
+    gbf = B200BigVGAN(sd, d["topology"], dtype=torch.bfloat16, device=DEV)
+    wavb = gbf.inference(feat, spk).clone()
+    perm = torch.randperm(B, generator=torch.Generator().manual_seed(1)).tolist()
+    wavp = gbf.inference(feat[perm], spk[perm])
+    for k, i in enumerate(perm):
+        assert torch.equal(wavp[k], wavb[i]), (k, i)
+    for i, want in d["wavs"].items():
+        err, snr = (wavb[i].cpu() - want).abs().max().item(), _snr_db(wavb[i].cpu(), want)
+        print(f"config 4 bf16 member {i}: max-abs {err:.3e}, SNR {snr:.1f} dB, peak {want.abs().max().item():.3f}")
+        assert err < 0.1 and snr > 30.0, (i, err, snr)
+
+
+# ----------------------------------------------------------------------------------------------- config 5 (ragged sweep) subset
+def test_config5_ragged_subset_members_equal_their_b1_runs_and_the_oracle():
+    """BASELINE config 5 on a 16-utterance subset drawn with the sweep's own seed (tools/bench_configs.py `sweep`: generated
+    duration ~ U[2, 30] s after a 3 s prompt, tokens = round(25 d)), batched exactly as the sweep batches them
+    (shard.make_batches: one stride bucket per batch) through AcousticBackend.synthesize_tokens_batch on the bf16 engine:
+      * the subset spans at least three stride buckets and the programs are re-bound across batches;
+      * every member's waveform equals its own B = 1 run bit for bit (the reference asserts B = 1, flow/flow.py:125);
+    and on the fp32 engine the shortest member (10 Euler steps) and the longest member (T ~ 3000 frames; 2 Euler steps to keep the
+    CPU oracle to seconds -- every step is the same computation) match the CPU oracle: mel max-abs < 2e-3, waveform with the
+    oracle's mel and an injected source < 1e-3."""
+    from cosyvoice_b200 import shard
+    from cosyvoice_b200.pipeline import AcousticBackend
+    HOP, PROMPT, N = 256, 281, 16
+    g = torch.Generator().manual_seed(2048)
+    dur = 2.0 + 28.0 * torch.rand(2048, generator=g)
+    n_tok = [int(round(25.0 * float(x))) for x in dur[:N]]
+    gen_frames = [int(n / 25 * SR / 256) for n in n_tok]
+    tot = [PROMPT + f for f in gen_frames]
+    batches = shard.make_batches(list(range(N)), tot, row_budget=48 * 1024, align=256, max_batch=64)
+    strides = {(tot[b[0]] + 8 + 255) // 256 * 256 for b in batches}
+    assert len(strides) >= 3 and sum(len(b) for b in batches) == N, (strides, batches)
+
+    def inputs(u):
+        t, pt, pf, e = init_weights.frontend_inputs(False, n_tok[u], 75, seed=1234 + u, sample_rate=SR)
+        return t, pt, pf, e, torch.randn(1, 80, tot[u], generator=torch.Generator().manual_seed(4321 + u))
+    fsd, esd, hsd = (init_weights.flow_frontend_sd(False, seed=2), init_weights.flow_estimator_sd(False, seed=0),
+                     init_weights.hift_sd(False, seed=1))
+    be = AcousticBackend(esd, hsd, v2=False, dtype=torch.bfloat16, device=DEV, frontend_sd=fsd)
+    wavs = {}
+    for b in batches:
+        cols = list(zip(*[inputs(u) for u in b]))
+        torch.manual_seed(99)                       # HiFT's own source RNG (phase / noise draws): same seed for the B = 1 runs
+        out = be.synthesize_tokens_batch(*[list(c) for c in cols], sample_rate=SR)
+        for u, w in zip(b, out):
+            assert w.shape == (1, gen_frames[u] * HOP) and torch.isfinite(w).all() and w.abs().max().item() <= 0.99 + 1e-6
+            wavs[u] = w.clone()
+    # B = 1: the flow is deterministic given z; HiFT draws its source noise from the global generator, whose stream
+    # depends on the batch composition, so the bit-for-bit comparison is made on the MEL and on the vocoder with an injected source
+    for b in batches:
+        cols = list(zip(*[inputs(u) for u in b]))
+        mels = [m.clone() for m in be.flow.inference_batch(*[list(c) for c in cols], 10, SR)]
+        L_max = max(gen_frames[u] for u in b) * HOP
+        src = torch.zeros(len(b), 1, L_max)
+        for k, u in enumerate(b):
+            src[k, :, :gen_frames[u] * HOP] = torch.randn(1, gen_frames[u] * HOP, generator=torch.Generator().manual_seed(7000 + u)) * 0.1
+        wb = [w.clone() for w in be.hift.inference_batch(mels, source=src, uniform_stride=True)[0]]
+        for k, u in enumerate(b):
+            one = be.flow.inference_batch(*[[c[k]] for c in cols], 10, SR)[0]
+            assert torch.equal(one, mels[k]), ("mel", u)
+            w1 = be.hift.inference_batch([one], source=src[k:k + 1, :, :gen_frames[u] * HOP], uniform_stride=True)[0][0]
+            assert torch.equal(w1, wb[k]), ("wav", u)
+    del be
+    # ---- fp32 engine against the CPU oracle: shortest (10 steps) and longest (2 steps) member
+    torch.set_flush_denormal(True)
+    be32 = AcousticBackend(esd, hsd, v2=False, dtype=torch.float32, device=DEV, frontend_sd=fsd)
+    order = sorted(range(N), key=lambda u: tot[u])
+    for u, steps in ((order[0], 10), (order[-1], 2)):
+        t, pt, pf, e, z = inputs(u)
+        mu, spks, cond, l1, l2 = encoder_ref.frontend_v1(fsd, t, pt, pf, e, sample_rate=SR)
+        assert (l1, l2) == (PROMPT, gen_frames[u])
+        want = flow_ref.solve_euler(esd, z, flow_ref.cosine_t_span(steps), mu, torch.ones(1, 1, l1 + l2), spks, cond)[:, :, l1:]
+        got = be32.flow.inference_batch([t], [pt], [pf], [e], [z], steps, SR)[0].cpu()
+        err = (got - want).abs().max().item()
+        src = torch.randn(1, 1, l2 * HOP, generator=torch.Generator().manual_seed(8)) * 0.1
+        want_w = hift_ref.decode(hsd, want, src, v2=False)
+        wav = be32.hift.inference_batch([want], source=src)[0][0].cpu()
+        werr = (wav - want_w).abs().max().item()
+        print(f"config 5 member {u} (T = {tot[u]}, {steps} Euler steps) fp32 vs oracle: mel {err:.3e}, waveform {werr:.3e}")
+        assert err < 2e-3 and werr < 1e-3, (u, err, werr)
