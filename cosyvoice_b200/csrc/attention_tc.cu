@@ -195,22 +195,29 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tm, __nv_bfloat16* __res
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
+    // whole warp, uniform state, one elected lane issues (ptx.cuh "lean issue path")
+    {
       const uint32_t idesc_qk = ptx::make_idesc_bf16(BQ, BK);                       // 128 x 128, A/B K-major
       const uint32_t idesc_pv = ptx::make_idesc_bf16(BQ, HD) | (1u << 16);          // 128 x 64, B MN-major
-      const uint32_t q_base = ptx::smem_u32(sQ);
+      const uint32_t kdesc_hi = (uint32_t)(ptx::make_sw128_kmajor_desc(0) >> 32);
+      const uint32_t vdesc_hi = (uint32_t)(make_sw128_mnmajor_desc(0) >> 32);
+      const uint32_t q_lo = (uint32_t)ptx::make_sw128_kmajor_desc(ptx::smem_u32(sQ));
+      const uint32_t k_lo0 = (uint32_t)ptx::make_sw128_kmajor_desc(ptx::smem_u32(sK));
+      const uint32_t v_lo0 = (uint32_t)make_sw128_mnmajor_desc(ptx::smem_u32(sV));
       auto issue_qk = [&](uint32_t gg) {
         const int st = gg % KV_STAGES;
         ptx::mbar_wait(&k_full[st], (gg / KV_STAGES) & 1);
         if (gg > 0) ptx::mbar_wait(s_free, (gg - 1) & 1);     // softmax has pulled S(g-1) out of TMEM
         ptx::tc_fence_after();
-        const uint32_t k_base = ptx::smem_u32(sK + st * TILE_BYTES);
+        const uint32_t k_lo = ptx::bcast0(k_lo0 + st * (TILE_BYTES >> 4));
+        if (ptx::elect_one()) {
 #pragma unroll
-        for (int k = 0; k < HD / 16; ++k)
-          ptx::umma_ss(tmem + TM_S, ptx::make_sw128_kmajor_desc(q_base + k * 32), ptx::make_sw128_kmajor_desc(k_base + k * 32),
-                       idesc_qk, k != 0);
-        ptx::umma_commit(&k_empty[st]);                       // the K stage is dead once this QK^T has retired
-        ptx::umma_commit(s_full);
+          for (int k = 0; k < HD / 16; ++k)
+            ptx::umma_ss_lo(tmem + TM_S, q_lo + k * 2, kdesc_hi, k_lo + k * 2, kdesc_hi, idesc_qk, k != 0);
+          ptx::umma_commit(&k_empty[st]);                       // the K stage is dead once this QK^T has retired
+          ptx::umma_commit(s_full);
+        }
+        __syncwarp();
       };
       uint32_t n = 0, g = 0;
       for (int it = blockIdx.x; it < n_items; it += gridDim.x) {
@@ -220,18 +227,25 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tm, __nv_bfloat16* __res
         issue_qk(g);
         for (int j = 0; j < w.nblk; ++j, ++g) {
           if (j + 1 < w.nblk) issue_qk(g + 1);
-          else ptx::umma_commit(q_free);                       // the item's last QK^T is in flight
+          else {
+            if (ptx::elect_one()) ptx::umma_commit(q_free);      // the item's last QK^T is in flight
+            __syncwarp();
+          }
           const int st = g % KV_STAGES;
           ptx::mbar_wait(p_full, g & 1);                       // P(g) is in TMEM, O has been rescaled
           if (j == 0 && n > 0) ptx::mbar_wait(o_free, (n - 1) & 1);   // previous item's O has been read out
           ptx::mbar_wait(&v_full[st], (g / KV_STAGES) & 1);
           ptx::tc_fence_after();
-          const uint32_t v_base = ptx::smem_u32(sV + st * TILE_BYTES);
+          const uint32_t v_lo = ptx::bcast0(v_lo0 + st * (TILE_BYTES >> 4));
+          const uint32_t acc0 = ptx::bcast0(j != 0);
+          if (ptx::elect_one()) {
 #pragma unroll
-          for (int k = 0; k < BK / 16; ++k)
-            ptx::umma_ts(tmem + TM_O, tmem + TM_P + k * 8, make_sw128_mnmajor_desc(v_base + k * 2048), idesc_pv, (j | k) != 0);
-          ptx::umma_commit(&v_empty[st]);
-          ptx::umma_commit(pv_done);
+            for (int k = 0; k < BK / 16; ++k)
+              ptx::umma_ts_lo(tmem + TM_O, tmem + TM_P + k * 8, v_lo + k * (2048 >> 4), vdesc_hi, idesc_pv, k == 0 ? acc0 : 1u);
+            ptx::umma_commit(&v_empty[st]);
+            ptx::umma_commit(pv_done);
+          }
+          __syncwarp();
         }
         ++n;
       }
@@ -245,6 +259,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tm, __nv_bfloat16* __res
     const int half = (warp - 2) >> 2;
     const int row = lane_grp * 32 + lane;
     const uint32_t tbase = tmem + ((uint32_t)(lane_grp * 32) << 16);
+    const uint32_t smax_addr = ptx::smem_u32(smax);
     uint32_t g = 0;
     for (int it = blockIdx.x; it < n_items; it += gridDim.x) {
       const AttnItem w = attn_item(lay, it, heads);
@@ -277,10 +292,14 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tm, __nv_bfloat16* __res
           mx4[3] = fmaxf(mx4[3], v[i + 3]);
         }
         const float m_loc = fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3]));
-        float* xch = smax + (g & 1) * 256;
-        xch[half * 128 + row] = m_loc;
-        ptx::named_bar_sync(1, 256);
-        const float m_new = fmaxf(m_run, fmaxf(m_loc, xch[(half ^ 1) * 128 + row]));
+        // the two halves of a row live in the two warps of a TMEM lane group: explicit shared-space accesses (the generic
+        // LD the compiler emitted for this exchange was the kernel's top stall) and a barrier of just those 64 threads
+        const uint32_t xch = smax_addr + (g & 1) * 1024;
+        asm volatile("st.shared.f32 [%0], %1;" ::"r"(xch + (half * 128 + row) * 4), "f"(m_loc) : "memory");
+        ptx::named_bar_sync(1 + lane_grp, 64);
+        float m_other;
+        asm volatile("ld.shared.f32 %0, [%1];" : "=f"(m_other) : "r"(xch + ((half ^ 1) * 128 + row) * 4) : "memory");
+        const float m_new = fmaxf(m_run, fmaxf(m_loc, m_other));
         const bool need = j == 0 || (m_new - m_use) * scale_log2 > RESCALE_LOG2;
         float corr = 1.f;
         if (need) {
@@ -326,10 +345,12 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tm, __nv_bfloat16* __res
         ptx::mbar_arrive(p_full);
       }
       // ---- epilogue: O / l -> bf16 (each thread writes 32 of the row's 64 output columns)
-      float* xch = smax + (g & 1) * 256;
-      xch[half * 128 + row] = l_half;
-      ptx::named_bar_sync(1, 256);
-      const float inv = 1.f / (l_half + xch[(half ^ 1) * 128 + row]);
+      const uint32_t xch = smax_addr + (g & 1) * 1024;
+      asm volatile("st.shared.f32 [%0], %1;" ::"r"(xch + (half * 128 + row) * 4), "f"(l_half) : "memory");
+      ptx::named_bar_sync(1 + lane_grp, 64);
+      float l_other;
+      asm volatile("ld.shared.f32 %0, [%1];" : "=f"(l_other) : "r"(xch + ((half ^ 1) * 128 + row) * 4) : "memory");
+      const float inv = 1.f / (l_half + l_other);
       ptx::mbar_wait(pv_done, (g - 1) & 1);
       ptx::tc_fence_after();
       const int lrow = w.q0 + row;

@@ -109,6 +109,18 @@ __global__ void __launch_bounds__(256) layernorm256_act_kernel(const void* __res
 }
 
 // ---------------------------------------------------------------------------- Norm + Mish (Block1D tail)
+// Mish for the bf16 engine: tanh(softplus(x)) = (u^2 + 2u) / (u^2 + 2u + 2) with u = e^x -- one MUFU.EX2 and one MUFU.RCP
+// instead of expf + log1pf + tanhf (relative error ~1e-6, far below the bf16 rounding of the output it feeds).
+__device__ __forceinline__ float mish_fast(float x) {
+  const float u = __expf(fminf(x, 20.f));
+  const float n = u * (u + 2.f);
+  return x > 20.f ? x : x * __fdividef(n, n + 2.f);
+}
+
+// ROWS rows per warp (all inside one 128-row tile = one sequence): the GroupNorm statistics are turned into (mean, rstd)
+// in fp64 ONCE per warp instead of once per row -- fp64 division and square root run at 1/64 rate on this part, and were
+// most of the 30 us this kernel took at 40 960 rows (round-1 launch list) for 42 MB of traffic.
+template <int ROWS>
 __global__ void __launch_bounds__(256) norm_mish256_kernel(const void* __restrict__ h, int ldh, int h_dt,
                                                            void* __restrict__ out, int ldo, int out_dt,
                                                            const float* __restrict__ gamma, const float* __restrict__ beta,
@@ -116,22 +128,23 @@ __global__ void __launch_bounds__(256) norm_mish256_kernel(const void* __restric
                                                            const float* __restrict__ seq_bias, int seq_bias_ld,
                                                            const Layout lay, float eps) {
   pdl_sync();
-  const int row = blockIdx.x * 8 + (threadIdx.x >> 5);
+  const int row0 = (blockIdx.x * 8 + (threadIdx.x >> 5)) * ROWS;
   const int lane = threadIdx.x & 31;
-  if (row >= lay.rows) return;
-  const int tile = row >> 7;
+  if (row0 >= lay.rows) return;
+  const int tile = row0 >> 7;
   const int b = __ldg(lay.tile_seq + tile);
-  const int lrow = __ldg(lay.tile_row0 + tile) + (row & 127);
+  const int lrow0 = __ldg(lay.tile_row0 + tile) + (row0 & 127);
   const int len = __ldg(lay.seq_len + b);
-  float v[8];
-  if (lrow >= len) {
+  float v[ROWS][8];
 #pragma unroll
-    for (int i = 0; i < 8; ++i) v[i] = 0.f;
-    store8(out, (size_t)row * ldo + lane * 8, out_dt, v);
-    return;
+  for (int r = 0; r < ROWS; ++r) {
+    if (lrow0 + r < len) load8_dt(h, (size_t)(row0 + r) * ldh + lane * 8, h_dt, v[r]);
+    else {
+#pragma unroll
+      for (int i = 0; i < 8; ++i) v[r][i] = 0.f;
+    }
   }
-  load8_dt(h, (size_t)row * ldh + lane * 8, h_dt, v);
-  float mean, rstd;
+  float gmean = 0.f, grstd = 0.f;
   if (gn_stats) {
     // GroupNorm(8, 256): group = 32 channels = 4 lanes; statistics over 32 channels x len frames
     const int g = lane >> 2;
@@ -140,32 +153,45 @@ __global__ void __launch_bounds__(256) norm_mish256_kernel(const void* __restric
     const double m = s / n;
     double var = q / n - m * m;
     if (var < 0.0) var = 0.0;
-    mean = (float)m;
-    rstd = (float)(1.0 / sqrt(var + (double)eps));
-#pragma unroll
-    for (int i = 0; i < 8; ++i) v[i] -= mean;
-  } else {
-    float s = 0.f;
-#pragma unroll
-    for (int i = 0; i < 8; ++i) s += v[i];
-    mean = warp_sum(s) * (1.f / 256.f);
-    float q = 0.f;
-#pragma unroll
-    for (int i = 0; i < 8; ++i) { v[i] -= mean; q += v[i] * v[i]; }
-    rstd = rsqrtf(warp_sum(q) * (1.f / 256.f) + eps);
+    gmean = (float)m;
+    grstd = (float)(1.0 / sqrt(var + (double)eps));
   }
-  float g8[8], b8[8];
+  float g8[8], b8[8], t8[8];
   load8<float>(gamma + lane * 8, g8);
   load8<float>(beta + lane * 8, b8);
+  if (seq_bias) load8<float>(seq_bias + (size_t)b * seq_bias_ld + lane * 8, t8);
+  const bool fast = out_dt == DT_BF16;
 #pragma unroll
-  for (int i = 0; i < 8; ++i) v[i] = mishf(v[i] * rstd * g8[i] + b8[i]);
-  if (seq_bias) {
-    float t8[8];
-    load8<float>(seq_bias + (size_t)b * seq_bias_ld + lane * 8, t8);
+  for (int r = 0; r < ROWS; ++r) {
+    if (lrow0 + r >= len) {                  // v[r] is zero: pad rows are written as zeros
+      store8(out, (size_t)(row0 + r) * ldo + lane * 8, out_dt, v[r]);
+      continue;
+    }
+    float mean = gmean, rstd = grstd;
+    if (gn_stats) {
 #pragma unroll
-    for (int i = 0; i < 8; ++i) v[i] += t8[i];
+      for (int i = 0; i < 8; ++i) v[r][i] -= mean;
+    } else {
+      float s = 0.f;
+#pragma unroll
+      for (int i = 0; i < 8; ++i) s += v[r][i];
+      mean = warp_sum(s) * (1.f / 256.f);
+      float q = 0.f;
+#pragma unroll
+      for (int i = 0; i < 8; ++i) { v[r][i] -= mean; q += v[r][i] * v[r][i]; }
+      rstd = rsqrtf(warp_sum(q) * (1.f / 256.f) + eps);
+    }
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const float y = v[r][i] * rstd * g8[i] + b8[i];
+      v[r][i] = fast ? mish_fast(y) : mishf(y);
+    }
+    if (seq_bias) {
+#pragma unroll
+      for (int i = 0; i < 8; ++i) v[r][i] += t8[i];
+    }
+    store8(out, (size_t)(row0 + r) * ldo + lane * 8, out_dt, v[r]);
   }
-  store8(out, (size_t)row * ldo + lane * 8, out_dt, v);
 }
 
 // ---------------------------------------------------------------------------- time embedding
@@ -411,8 +437,12 @@ int launch_norm_mish(const void* h, int ldh, int h_dt, void* out, int ldo, int o
   CVB_REQUIRE(C == 256, "Norm+Mish kernel is specialised for 256 channels");
   CVB_REQUIRE(ldh % 8 == 0 && ldo % 8 == 0, "leading dimensions must keep 16-byte alignment");
   if (lay.rows <= 0) return CVB_OK;
-  CVB_CUDA(launch_pdl(norm_mish256_kernel, dim3(ceil_div(lay.rows, 8)), dim3(256), 0, st, h, ldh, h_dt, out, ldo, out_dt, gamma, beta, gn_stats,
-                                                             seq_bias, seq_bias_ld, lay, eps));
+  if (lay.rows >= 16384)
+    CVB_CUDA(launch_pdl(norm_mish256_kernel<4>, dim3(ceil_div(lay.rows, 32)), dim3(256), 0, st, h, ldh, h_dt, out, ldo, out_dt, gamma,
+                        beta, gn_stats, seq_bias, seq_bias_ld, lay, eps));
+  else
+    CVB_CUDA(launch_pdl(norm_mish256_kernel<1>, dim3(ceil_div(lay.rows, 8)), dim3(256), 0, st, h, ldh, h_dt, out, ldo, out_dt, gamma,
+                        beta, gn_stats, seq_bias, seq_bias_ld, lay, eps));
   CVB_LAUNCH_CHECK();
   return CVB_OK;
 }

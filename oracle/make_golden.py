@@ -170,9 +170,19 @@ def bigvgan_config4(members=(0, 31, 63), B=64, frames=94):
     _save("bigvgan_config4.pt", dict(weights_seed=3, topology="24k100", input_seed=5, batch=B, frames=frames, wavs=wavs))
 
 
+FORK_POST_GAIN = 0.05     # see bigvgan(): keeps the fork topology's synthetic output out of tanh saturation
+
+
 def bigvgan(topology="24k100"):
     m = R.build_bigvgan(topology).eval()
     sd = W.bigvgan_sd(topology, seed=2)
+    post_gain = 1.0
+    if topology == "fork":
+        # with the synthetic weights the 1024-channel input drives conv_post far into tanh saturation (rms 0.92): a clipped
+        # waveform pins nothing.  Both sides scale conv_post's weight-norm gain; the fixture records the factor.
+        post_gain = FORK_POST_GAIN
+        sd["conv_post.weight_g"] = sd["conv_post.weight_g"] * post_gain
+        sd["conv_post.bias"] = sd["conv_post.bias"] * post_gain
     res = m.load_state_dict(sd, strict=False)
     assert not res.unexpected_keys, res.unexpected_keys
     allowed = ("input_embedding.", "encoder_proj.", "mel_proj.")
@@ -184,7 +194,7 @@ def bigvgan(topology="24k100"):
     feat = torch.randn(B, in_ch, T, generator=g)
     spk = torch.randn(B, 512, 1, generator=g)
     wav = _bigvgan_trunk(m, feat, spk)
-    _save(f"bigvgan_{topology}.pt", dict(weights_seed=2, topology=topology, feat=feat, spk=spk, wav=wav))
+    _save(f"bigvgan_{topology}.pt", dict(weights_seed=2, topology=topology, feat=feat, spk=spk, wav=wav, post_gain=post_gain))
 
 
 def token2wav():
