@@ -45,11 +45,19 @@ def _pad64(c: int) -> int:
 
 
 class _AmpW:
-    """AMPBlock1 (bigvgan.py:32-143): 3 x (act, dilated conv, act, conv) with residual."""
+    """AMPBlock1 (bigvgan.py:32-143): 3 x (act, dilated conv, act, conv) with residual; AMPBlock2 (bigvgan.py:146-232,
+    selected by `resblock: "2"`): 3 x (act, dilated conv) with residual.  The block type is read off the state_dict keys."""
 
     def __init__(self, sd: SD, p: str, k: int, dtype, device):
         f32 = lambda key: sd[key].detach().float().to(device).contiguous()
         self.convs1, self.convs2, self.acts = [], [], []
+        self.kind = 2 if f"{p}convs.0.bias" in sd else 1
+        if self.kind == 2:
+            for i, d in enumerate((1, 3, 5)):
+                self.convs1.append(conv1d_plan(fold_weight_norm(sd, f"{p}convs.{i}."), sd[f"{p}convs.{i}.bias"], dtype, device,
+                                               dilation=d))
+                self.acts.append((f32(f"{p}activations.{i}.act.alpha"), f32(f"{p}activations.{i}.act.beta")))
+            return
         for i, d in enumerate((1, 3, 5)):
             self.convs1.append(conv1d_plan(fold_weight_norm(sd, f"{p}convs1.{i}."), sd[f"{p}convs1.{i}.bias"], dtype,
                                            device, dilation=d))
@@ -115,6 +123,16 @@ class _Program:
     def _amp(self, rb: _AmpW, L, c, xin, av, bv, xr, final: dict):
         g = self.g
         x_cur = xin
+        if rb.kind == 2:                      # AMPBlock2.forward (bigvgan.py:223-228): x = conv_d(act(x)) + x
+            for j in range(3):
+                a1, b1 = rb.acts[j]
+                self.ops.append(lambda x=x_cur, a1=a1, b1=b1: ops.anti_alias_act_rows(x, av, g.filt, a1, b1, c, L))
+                if j < 2:
+                    self._gemm(rb.convs1[j], av, L, xr, res=x_cur)
+                    x_cur = xr
+                else:
+                    self._gemm(rb.convs1[j], av, L, final.pop("out0"), res=x_cur, **final)
+            return
         for j in range(3):
             a1, b1 = rb.acts[2 * j]
             a2, b2 = rb.acts[2 * j + 1]

@@ -178,8 +178,9 @@ def hift_sd(v2: bool, seed: int = 0) -> SD:
 
 
 # ----------------------------------------------------------------------------- BigVGAN trunk
-def bigvgan_sd(topology: str = "24k100", seed: int = 0) -> SD:
-    """Trunk parameters only (conv_pre, cond layers, ups, AMP blocks, activation_post, conv_post)."""
+def bigvgan_sd(topology: str = "24k100", seed: int = 0, resblock: str = "1") -> SD:
+    """Trunk parameters only (conv_pre, cond layers, ups, AMP blocks, activation_post, conv_post).  resblock "1" = AMPBlock1
+    (convs1 / convs2, six activations per block), "2" = AMPBlock2 (convs, three activations; BigVGAN/bigvgan.py:146-232)."""
     g = _g(seed)
     sd: SD = {}
     if topology == "24k100":
@@ -201,11 +202,11 @@ def bigvgan_sd(topology: str = "24k100", seed: int = 0) -> SD:
         sd[f"conds.{i}.bias"] = _bias(g, cout, 0.02)
         for j, rk in enumerate((3, 7, 11)):
             p = f"resblocks.{i * 3 + j}."
-            for name in ("convs1", "convs2"):
+            for name in (("convs1", "convs2") if resblock == "1" else ("convs",)):
                 for d in range(3):
                     _wn(g, sd, f"{p}{name}.{d}.", (cout, cout, rk), std=0.02)
                     sd[f"{p}{name}.{d}.bias"] = _bias(g, cout, 0.02)
-            for a in range(6):
+            for a in range(6 if resblock == "1" else 3):
                 sd[f"{p}activations.{a}.act.alpha"] = 0.3 * torch.randn(cout, generator=g)
                 sd[f"{p}activations.{a}.act.beta"] = 0.3 * torch.randn(cout, generator=g)
     ch = ch0 // 2 ** len(rates)

@@ -83,6 +83,15 @@ def _ampblock1(sd: SD, p: str, x, k: int, filt, dils=(1, 3, 5)):
     return x
 
 
+def _ampblock2(sd: SD, p: str, x, k: int, filt, dils=(1, 3, 5)):
+    """AMPBlock2.forward, BigVGAN/bigvgan.py:223-228: one dilated conv per layer, x = conv(act(x)) + x."""
+    for i, d in enumerate(dils):
+        xt = anti_alias_act(x, sd[f"{p}activations.{i}.act.alpha"], sd[f"{p}activations.{i}.act.beta"], filt)
+        xt = F.conv1d(xt, wn(sd, f"{p}convs.{i}."), sd[f"{p}convs.{i}.bias"], dilation=d, padding=(k * d - d) // 2)
+        x = xt + x
+    return x
+
+
 def trunk_forward(sd: SD, feat, spk, topology: str = "24k100", taps: Optional[dict] = None):
     """bigvgan.py:406-436.  feat [B,C_in,T] (the encoder_proj output), spk [B,512,1] -> wav [B,L]."""
     a = arch(topology)
@@ -94,7 +103,8 @@ def trunk_forward(sd: SD, feat, spk, topology: str = "24k100", taps: Optional[di
         x = x + F.conv1d(spk, sd[f"conds.{i}.weight"], sd[f"conds.{i}.bias"])
         xs = None
         for j, rk in enumerate((3, 7, 11)):
-            r = _ampblock1(sd, f"resblocks.{i * 3 + j}.", x, rk, filt)
+            p = f"resblocks.{i * 3 + j}."
+            r = (_ampblock2 if f"{p}convs.0.bias" in sd else _ampblock1)(sd, p, x, rk, filt)
             xs = r if xs is None else xs + r
         x = xs / 3
         if taps is not None:

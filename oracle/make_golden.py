@@ -173,9 +173,9 @@ def bigvgan_config4(members=(0, 31, 63), B=64, frames=94):
 FORK_POST_GAIN = 0.05     # see bigvgan(): keeps the fork topology's synthetic output out of tanh saturation
 
 
-def bigvgan(topology="24k100"):
-    m = R.build_bigvgan(topology).eval()
-    sd = W.bigvgan_sd(topology, seed=2)
+def bigvgan(topology="24k100", resblock="1"):
+    m = R.build_bigvgan(topology, resblock).eval()
+    sd = W.bigvgan_sd(topology, seed=2, resblock=resblock)
     post_gain = 1.0
     if topology == "fork":
         # with the synthetic weights the 1024-channel input drives conv_post far into tanh saturation (rms 0.92): a clipped
@@ -194,7 +194,8 @@ def bigvgan(topology="24k100"):
     feat = torch.randn(B, in_ch, T, generator=g)
     spk = torch.randn(B, 512, 1, generator=g)
     wav = _bigvgan_trunk(m, feat, spk)
-    _save(f"bigvgan_{topology}.pt", dict(weights_seed=2, topology=topology, feat=feat, spk=spk, wav=wav, post_gain=post_gain))
+    name = f"bigvgan_{topology}.pt" if resblock == "1" else f"bigvgan_{topology}_amp{resblock}.pt"
+    _save(name, dict(weights_seed=2, topology=topology, resblock=resblock, feat=feat, spk=spk, wav=wav, post_gain=post_gain))
 
 
 def token2wav():
@@ -324,6 +325,7 @@ if __name__ == "__main__":
     act1d()
     bigvgan("24k100")
     bigvgan("fork")
+    bigvgan("24k100", resblock="2")
     bigvgan_config4()
     token2wav()
     frontend(False)

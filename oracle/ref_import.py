@@ -75,18 +75,18 @@ def build_hift(v2: bool):
                          source_resblock_dilation_sizes=[[1, 3, 5]] * 2, **kw)
 
 
-def build_bigvgan(topology: str = "24k100"):
+def build_bigvgan(topology: str = "24k100", resblock: str = "1"):
     """BigVGAN trunk; encoders left None (out of scope)."""
     setup()
     from cosyvoice.BigVGAN.bigvgan import BigVGAN
     if topology == "24k100":
         return BigVGAN(output_size=100, upsample_rates=[4, 4, 2, 2, 2, 2],
                        upsample_kernel_sizes=[8, 8, 4, 4, 4, 4], upsample_initial_channel=1536,
-                       speaker_embedding_dim=512)
+                       speaker_embedding_dim=512, resblock=resblock)
     if topology == "fork":
         return BigVGAN(output_size=1024, upsample_rates=[8, 5, 3, 2],
                        upsample_kernel_sizes=[16, 11, 7, 2], upsample_initial_channel=1536,
-                       speaker_embedding_dim=512)
+                       speaker_embedding_dim=512, resblock=resblock)
     raise ValueError(topology)
 
 

@@ -215,6 +215,26 @@ def test_bigvgan_fork_topology_matches_reference_golden(golden_dir):
     assert errb < 0.05 and snr > 30.0, (errb, snr)
 
 
+def test_bigvgan_ampblock2_matches_reference_golden(golden_dir):
+    """AMPBlock2 (BigVGAN/bigvgan.py:146-232, `resblock: "2"`: one dilated conv per layer) on the 24 kHz / 100-band trunk against
+    the REAL reference's recording: fp32 < 2e-4, bf16 (tcgen05) within 0.05 / SNR > 30 dB."""
+    from cosyvoice_b200.bigvgan import B200BigVGAN
+    d = _load(golden_dir, "bigvgan_24k100_amp2.pt")
+    assert d["resblock"] == "2"
+    sd = init_weights.bigvgan_sd(d["topology"], seed=d["weights_seed"], resblock="2")
+    g32 = B200BigVGAN(sd, d["topology"], dtype=torch.float32, device=DEV)
+    wav = g32.inference(d["feat"], d["spk"]).cpu()
+    err = (wav - d["wav"]).abs().max().item()
+    print(f"BigVGAN AMPBlock2 fp32: max-abs {err:.3e}")
+    assert wav.shape == d["wav"].shape and err < 2e-4, err
+    gbf = B200BigVGAN(sd, d["topology"], dtype=torch.bfloat16, device=DEV)
+    wavb = gbf.inference(d["feat"], d["spk"]).cpu()
+    errb = (wavb - d["wav"]).abs().max().item()
+    snr = (10 * torch.log10(d["wav"].pow(2).mean() / (wavb - d["wav"]).pow(2).mean())).item()
+    print(f"BigVGAN AMPBlock2 bf16: max-abs {errb:.3e}, SNR {snr:.1f} dB")
+    assert errb < 0.05 and snr > 30.0, (errb, snr)
+
+
 @pytest.mark.parametrize("ver", ["v1", "v2"])
 def test_hift_program_rebinds_lengths(golden_dir, ver):
     """Streaming reuse: one program per 128-frame stride bucket serves longer and then shorter mels; the stale rows

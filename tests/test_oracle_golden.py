@@ -80,6 +80,19 @@ def test_anti_alias_activation_matches_reference(golden_dir):
     _close(bigvgan_ref.anti_alias_act(d["x"], d["alpha"], d["beta"]), d["y"], atol=2e-6)
 
 
+def test_bigvgan_oracle_on_the_fork_topology_and_ampblock2(golden_dir):
+    """oracle/bigvgan_ref.py pinned on the fork's own topology ([8,5,3,2], 1024-channel input; conv_post gain as recorded) and
+    on AMPBlock2, against recordings of the REAL reference trunk (oracle/make_golden.py)."""
+    d = _load(golden_dir, "bigvgan_fork.pt")
+    sd = init_weights.bigvgan_sd("fork", seed=d["weights_seed"])
+    sd["conv_post.weight_g"] = sd["conv_post.weight_g"] * d["post_gain"]
+    sd["conv_post.bias"] = sd["conv_post.bias"] * d["post_gain"]
+    _close(bigvgan_ref.trunk_forward(sd, d["feat"], d["spk"], "fork"), d["wav"], atol=5e-5)
+    d = _load(golden_dir, "bigvgan_24k100_amp2.pt")
+    sd = init_weights.bigvgan_sd(d["topology"], seed=d["weights_seed"], resblock="2")
+    _close(bigvgan_ref.trunk_forward(sd, d["feat"], d["spk"], d["topology"]), d["wav"], atol=2e-5)
+
+
 def test_bigvgan_trunk_matches_reference(golden_dir):
     d = _load(golden_dir, "bigvgan_24k100.pt")
     sd = init_weights.bigvgan_sd(d["topology"], seed=d["weights_seed"])
