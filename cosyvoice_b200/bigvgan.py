@@ -85,9 +85,9 @@ class _Program:
         self.ops: List[ops.Op] = []
         self.flops = 0
         # speaker conditioning: 1x1 convs on spk [B,512,1] = per-sequence biases (bigvgan.py:407,417-418)
-        self.ops.append(lambda: ops.small_linear(self.spk, g.cond_w, g.cond_b, self.cond0))
+        self.ops.append(lambda spk=self.spk, c0=self.cond0: ops.small_linear(spk, g.cond_w, g.cond_b, c0))
         for i in range(len(chs)):
-            self.ops.append(lambda i=i: ops.small_linear(self.spk, g.conds_w[i], g.conds_b[i], self.conds[i]))
+            self.ops.append(lambda i=i, spk=self.spk, c=self.conds[i]: ops.small_linear(spk, g.conds_w[i], g.conds_b[i], c))
         x_prev = z(lay0.rows, a["ch0"])
         self._gemm(g.conv_pre, self.feat, lay0, x_prev, seq_bias=self.cond0)
         lay_prev, P = lay0, 1
@@ -185,7 +185,7 @@ class B200BigVGAN:
         key = tuple(int(l) for l in lens)
         if key not in self._programs:
             if len(self._programs) >= 4:
-                self._programs.pop(next(iter(self._programs))).__dict__.clear()
+                self._programs.pop(next(iter(self._programs)))      # holders of the evicted program keep it alive
             self._programs[key] = _Program(self, key)
         return self._programs[key]
 

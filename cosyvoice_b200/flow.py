@@ -27,6 +27,7 @@ SD = Dict[str, torch.Tensor]
 C = 256           # estimator width
 HEADS, HEAD_DIM = 8, 64
 TIME_DIM = 1024
+FUSED_FFN_MIN_TILES = 48      # row tiles (128 rows) from which block_ffn beats LN + FF1 + FF2 + LN (see _Program._stage)
 N_FEATS = 80
 
 
@@ -138,7 +139,13 @@ class _Program:
         causal = w.causal
         # Fused second half of a transformer block (csrc/block_ffn_tc.cu): norm3 + FeedForward + residual (+ the next
         # block's norm1) in one kernel on the bf16 residual stream.  CVB200_FUSED_FFN=0 restores the four separate launches.
-        self.fused_ffn = engine == _lib.ENGINE_TCGEN05 and os.environ.get("CVB200_FUSED_FFN", "1") == "1"
+        # CVB200_FUSED_FFN = auto (default: by layout size, see _stage) | 1 (every layout) | 0 (never).  Pinning it to 0 or 1
+        # makes a batch member bit-identical to its own B = 1 call (same kernels at every size).
+        mode = os.environ.get("CVB200_FUSED_FFN", "auto")
+        if mode not in ("auto", "0", "1"):
+            raise ValueError(f"CVB200_FUSED_FFN must be auto, 0 or 1 (got {mode!r})")
+        self.fused_ffn = engine == _lib.ENGINE_TCGEN05 and mode != "0"
+        self.fused_ffn_min_tiles = FUSED_FFN_MIN_TILES if mode == "auto" else 1
         R, S = lay.rows, lay.n_seq
         z = lambda *shape, dtype=dt: torch.zeros(*shape, dtype=dtype, device=dev)
         self.t = z(S, dtype=torch.float32)
@@ -260,9 +267,13 @@ class _Program:
             self.taps["down0.resnet"] = (self.X, L)
         qkv, o, f = self.qkv[:R], self.o[:R], self.f[:R]
         n_tb = len(st["tbs"])
-        # Fused second half (norm3 + FFN + residual, one kernel).  Chosen by the engine only, never by the problem size: a
-        # batch member must equal its own B = 1 run bit for bit (tests/test_gpu_fullsize.py), so both take the same kernels.
-        fuse = self.fused_ffn and X.dtype == torch.bfloat16 and all(t["ffw"] is not None for t in st["tbs"])
+        # Fused second half (norm3 + FFN + residual, one kernel) from FUSED_FFN_MIN_TILES 128-row tiles up.  One CTA owns
+        # a tile's whole FFN (27 us alone), while the separate GEMMs spread a small problem over all SMs by output
+        # column: below ~40 tiles the four launches win inside a CUDA graph (streaming chunk 30.6 vs 34.3 ms,
+        # profiles/r02_ffn_rows_sweep.txt).  The choice depends on the STRIDE pattern only (L.m_tiles), so every call of
+        # a program takes the same kernels and batch members stay independent of their neighbours.
+        fuse = (self.fused_ffn and X.dtype == torch.bfloat16 and L.m_tiles >= self.fused_ffn_min_tiles
+                and all(t["ffw"] is not None for t in st["tbs"]))
         stats = self.row_stats[:R]
         for k, t in enumerate(st["tbs"]):
             # components/transformer.py:262-316

@@ -168,7 +168,7 @@ class _Program:
         if w.f0_split_convs and engine == _lib.ENGINE_TCGEN05:
             self.msplit = z(R0, 3 * 128)
             self.hsplit = z(R0, 3 * 512)
-            self.ops_f0.append(lambda: ops.split3_bf16(self.mel32, self.msplit, 80, 128))
+            self.ops_f0.append(lambda m=self.mel32, d=self.msplit: ops.split3_bf16(m, d, 80, 128))
             a_in = self.msplit
             for i, (plan, plan32) in enumerate(zip(w.f0_split_convs, w.f0_convs)):
                 fl = plan32.flops_per_row * sum(lay0.lens)          # algorithmic FLOPs of the conv, not of the 6 terms
@@ -176,7 +176,7 @@ class _Program:
                                                flops=fl))
                 self.flops += fl
                 if i + 1 < len(w.f0_split_convs):
-                    self.ops_f0.append(lambda: ops.split3_bf16(self.fa, self.hsplit, 512, 512))
+                    self.ops_f0.append(lambda m=self.fa, d=self.hsplit: ops.split3_bf16(m, d, 512, 512))
                 a_in = self.hsplit
             src = self.fa
         else:
@@ -187,13 +187,13 @@ class _Program:
                 self.flops += fl
                 src, dst = dst, (self.fb if dst is self.fa else self.fa)
         f0_in = src
-        self.ops_f0.append(lambda: ops.rowdot_abs(f0_in, w.f0_w, w.f0_b, self.f0, R0))
+        self.ops_f0.append(lambda f0=self.f0: ops.rowdot_abs(f0_in, w.f0_w, w.f0_b, f0, R0))
         # ---- source: f0 -> s (generator.py:404-406)
         self.ops_src: List[ops.Op] = [
-            lambda: ops.sine_source(self.f0, lay0, w.hop, float(sampling_rate), self.noise, self.phase, w.src_w, w.src_b,
-                                    self.prefix, self.s)]
+            lambda f0=self.f0, nz=self.noise, ph=self.phase, pre=self.prefix, s=self.s: ops.sine_source(
+                f0, lay0, w.hop, float(sampling_rate), nz, ph, w.src_w, w.src_b, pre, s)]
         # ---- decode (generator.py:349-381)
-        self.ops.append(lambda: ops.stft16(self.s, self.sst, lay_f))
+        self.ops.append(lambda s=self.s, sst=self.sst: ops.stft16(s, sst, lay_f))
         self.x0 = z(R0, 512)
         self._gemm(w.conv_pre, self.mel, lay0, self.x0, act=_lib.ACT_LRELU, act_slope=0.1)
         x_prev, lay_prev = self.x0, lay0
@@ -233,11 +233,12 @@ class _Program:
         self.cp = z(lay_f.rows, 32, dtype=f32)
         self._gemm(w.conv_post, x_prev, lay_f, self.cp)
         self.marks["conv_post"] = (len(self.ops), self.cp, lay_f)
-        self.ops.append(lambda: ops.istft16(self.cp, lay_f, self.wav, float(audio_limit)))
+        self.ops.append(lambda cp=self.cp, wav=self.wav: ops.istft16(cp, lay_f, wav, float(audio_limit)))
 
     def release(self):
-        """Drop buffers and launch closures (they reference each other in cycles: without this an evicted program
-        keeps its HBM until the next Python gc pass)."""
+        """Drop buffers and launch closures at once (explicit teardown for an owner that knows nobody else holds the
+        program).  The launch closures bind buffers, never the program itself, so a program that merely falls out of
+        the LRU cache is reclaimed by reference counting as soon as its last holder lets go."""
         self.__dict__.clear()
 
     def set_lens(self, lens: Sequence[int]):

@@ -73,6 +73,7 @@ def _profiled(kind: str, flops: int, fn):
         fn()
         e1.record()
         PROFILE.append((kind, flops, e0, e1))
+    run.kind = kind          # which kernel family this launch belongs to (tests and bench breakdowns read it)
     return run
 
 

@@ -106,11 +106,25 @@ def test_cfm_v2_fp32_golden_and_fixed_noise(golden_dir):
     assert (mel.cpu() - d["mel"]).abs().max().item() < 2e-3
 
 
+@pytest.mark.parametrize("ffn", ["by_size", "fused"])
 @pytest.mark.parametrize("ver", ["v1", "v2"])
-def test_cfm_bf16_tcgen05_within_bound(golden_dir, ver):
+def test_cfm_bf16_tcgen05_within_bound(golden_dir, ver, ffn, monkeypatch):
+    """Both FFN paths of the bf16 engine against the real reference's mel: the four launches a layout this small
+    selects, and block_ffn (folded LayerNorm, hidden tensor in TMEM) forced onto the same small layout."""
     d = _load(golden_dir, f"cfm_{ver}.pt")
     causal = d["causal"]
-    est = _estimator(causal, torch.bfloat16, _lib.ENGINE_TCGEN05)
+    if ffn == "fused":
+        monkeypatch.setenv("CVB200_FUSED_FFN", "1")
+        est = B200Estimator(init_weights.flow_estimator_sd(causal, seed=0), causal=causal, dtype=torch.bfloat16, device=DEV,
+                            engine=_lib.ENGINE_TCGEN05)
+        with torch.inference_mode():
+            names = [getattr(op, "kind", "") for op in est.program(est.layout_for([d["mu"].shape[-1]] * 2)).ops]
+        assert "block_ffn" in names, names
+    else:
+        est = _estimator(causal, torch.bfloat16, _lib.ENGINE_TCGEN05)
+        with torch.inference_mode():
+            names = [getattr(op, "kind", "") for op in est.program(est.layout_for([d["mu"].shape[-1]] * 2)).ops]
+        assert "block_ffn" not in names, names
     cfm = (B200CausalConditionalCFM if causal else B200ConditionalCFM)(est)
     mel = cfm.solve_batch([d["mu"]], [d["spks"]], [d["cond"]], [d["z"]], 10)[0].cpu()
     assert _rel_rms(mel, d["mel"]) < BF16_REL_RMS, _rel_rms(mel, d["mel"])
@@ -163,3 +177,19 @@ def test_program_rebinds_lengths_under_one_stride_bucket(causal):
         if n_prog0 is None:
             n_prog0 = len(cfm._graphs)
     assert len(cfm._graphs) == n_prog0        # one graph served all three lengths
+
+
+def test_evicted_estimator_programs_are_reclaimed_by_reference_counting():
+    """Programs dropped from the LRU cache (32 entries) go away by reference counting alone -- no cycle through the
+    launch list -- so a ragged sweep does not pile dead programs up in HBM between Python gc passes."""
+    import gc
+    import weakref
+    est = B200Estimator(init_weights.flow_estimator_sd(False, seed=0), causal=False, dtype=torch.bfloat16, device=DEV)
+    gc.collect()
+    gc.disable()
+    try:
+        refs = [weakref.ref(est.program(est.layout_for([100 + 256 * k]))) for k in range(34)]
+        assert refs[0]() is None and refs[1]() is None
+        assert all(r() is not None for r in refs[2:])
+    finally:
+        gc.enable()
