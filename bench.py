@@ -307,10 +307,11 @@ def run_ours(args):
     # dram__bytes_read.sum,dram__bytes_write.sum` over the GEMM launches of two estimator calls of this workload)
     traffic, traffic_src = None, None
     try:
-        with open(os.path.join(ROOT, "profiles", "r01_dram_traffic_per_launch.json")) as f:
+        with open(os.path.join(ROOT, "profiles", "r02_dram_traffic_per_launch.json")) as f:
             tj = json.load(f)["gemm"]
         traffic = tj["dram_read_bytes_per_launch"] + tj["dram_write_bytes_per_launch"]
-        traffic_src = "profiles/r01_dram_traffic_per_launch.json (ncu, mean over %d launches)" % tj["launches"]
+        traffic_src = ("profiles/r02_dram_traffic_per_launch.json (ncu dram__bytes_read.sum + dram__bytes_write.sum, mean over "
+                       "the %d estimator launches of tools/profile_step.py --timesteps 2)" % tj["launches"])
     except Exception:
         pass
     out = {
@@ -335,7 +336,7 @@ def run_ours(args):
                      "kernels": {k: {"launches": d["launches"], "ms": round(d["ms"], 3),
                                      "tflops": round(d["flops"] / max(d["ms"], 1e-9) / 1e9, 1)}
                                  for k, d in prof.items() if isinstance(d, dict)},
-                     "attention": {"kernel": "attention_tc_kernel (tcgen05/TMEM flash)", "launches": att["launches"],
+                     "attention": {"kernel": "attention_tc2_kernel (tcgen05/TMEM flash, two 128-query slots per CTA)", "launches": att["launches"],
                                    "ms": att["ms"], "achieved_tflops": att["flops"] / (att["ms"] * 1e-3) / 1e12,
                                    "share_of_eager_step": att["ms"] / prof["_step_ms_eager"]}},
     }
