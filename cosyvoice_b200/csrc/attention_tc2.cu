@@ -33,22 +33,42 @@ int device_sm_count();        // tapgemm_tc.cu
 
 namespace {
 
-constexpr int HD = 64, BQ = 128, BK = 128;
-constexpr int TILE_BYTES = 128 * 64 * 2;            // 16 KiB
+#ifndef ATTN2_SLOTS
+#define ATTN2_SLOTS 2
+#endif
+#ifndef ATTN2_BK
+#define ATTN2_BK 128
+#endif
+constexpr int HD = 64, BQ = 128, BK = ATTN2_BK;     // BK: keys per block (64 or 128)
+constexpr int SLOTS = ATTN2_SLOTS;
+static_assert(BK == 64 || BK == 128, "key block = 64 or 128");
+constexpr int CH = BK / 32;                          // 32-column chunks of a row of S
+constexpr int Q_BYTES = BQ * HD * 2;                 // 16 KiB
+constexpr int KV_BYTES = BK * HD * 2;                // 8 / 16 KiB
 constexpr int KV_STAGES = 2;
-constexpr int SLOTS = 2;
 constexpr int Q_BUFS = 2;                                            // the next item's Q tile is fetched during the current item
-constexpr int SLOT_SMEM = TILE_BYTES * (Q_BUFS + 2 * KV_STAGES);     // Q x 2 + K ring + V ring = 96 KiB
+constexpr int SLOT_SMEM = Q_BYTES * Q_BUFS + 2 * KV_BYTES * KV_STAGES;     // Q x 2 + K ring + V ring
 constexpr int SLOT_BARS = 20;                                        // mbarriers per slot
 constexpr int MAX_ITEMS = 256;                                       // per slot: the CTA's item table lives in shared memory
 constexpr int SMEM_BYTES = 1024 + SLOTS * SLOT_SMEM + SLOTS * SLOT_BARS * 8 + 64 + SLOTS * MAX_ITEMS * 16;
-#ifndef ATTN2_XU_LOCK
-#define ATTN2_XU_LOCK 0
-#endif
-constexpr int TM_S = 0, TM_P = 128, TM_O = 192, TM_SLOT = 256, TM_COLS = 512;
-constexpr int NUM_THREADS = SLOTS * (128 + 64);
-// warps 0 .. 4*SLOTS-1: softmax; then per slot a loader warp and an MMA warp (one control warp per scheduler)
+static_assert(SMEM_BYTES <= 227 * 1024, "shared memory");
+// TMEM columns of a slot: S [0, BK) fp32, P [BK, BK + BK/2) packed bf16, O [.., +64) fp32
+constexpr int TM_S = 0, TM_P = BK, TM_O = BK + BK / 2, TM_SLOT = BK + BK / 2 + HD, TM_COLS = 512;
+static_assert(SLOTS * TM_SLOT <= TM_COLS, "TMEM columns");
+// warps 0 .. 4*SLOTS-1: softmax (one warpgroup per slot); then the control warps, rounded up to whole warpgroups: per slot a
+// loader warp and an MMA warp; the rest idle
 constexpr int CTRL_WARP0 = SLOTS * 4, MMA_WARP = CTRL_WARP0 + 1;
+constexpr int CTRL_WARPS = (2 * SLOTS + 3) / 4 * 4;
+constexpr int NUM_THREADS = 32 * (CTRL_WARP0 + CTRL_WARPS);
+// Register budget (setmaxnreg, per warpgroup): the kernel launches with the average budget, the control warpgroups drop to
+// CTRL_REGS and every softmax warpgroup takes SOFTMAX_REGS (a softmax thread keeps a whole row of S in registers).
+// setmaxnreg only moves registers inside the CTA's own pool (what the control warps give back), so
+//   softmax threads x (SOFTMAX_REGS - LAUNCH_REGS) <= control threads x (LAUNCH_REGS - CTRL_REGS);
+// asking for more faults the launch (seen with 3 slots: "unspecified launch failure").
+constexpr int LAUNCH_REGS = 65536 / NUM_THREADS / 8 * 8;            // what __launch_bounds__(NUM_THREADS, 1) compiles to
+constexpr int CTRL_REGS = 56;
+constexpr int SOFTMAX_REGS_ = LAUNCH_REGS + (32 * CTRL_WARPS * (LAUNCH_REGS - CTRL_REGS)) / (128 * SLOTS) / 8 * 8;
+constexpr int SOFTMAX_REGS = SOFTMAX_REGS_ > 232 ? 232 : SOFTMAX_REGS_;
 
 // MN-major 128B-swizzled shared-memory operand (V tile: rows = keys (K dim), 64 d (N dim) contiguous = 128 B).
 __device__ __forceinline__ uint64_t make_sw128_mnmajor_desc(uint32_t smem_addr) {
@@ -134,14 +154,14 @@ struct Cursor {
 };
 
 __global__ void __launch_bounds__(NUM_THREADS, 1)
-attention_tc2_kernel(const __grid_constant__ CUtensorMap tm, __nv_bfloat16* __restrict__ out, int ldo, const Layout lay,
+attention_tc2_kernel(const __grid_constant__ CUtensorMap tm, const __grid_constant__ CUtensorMap tmkv,
+                     __nv_bfloat16* __restrict__ out, int ldo, const Layout lay,
                      int heads, float scale_log2, int n_items) {
   const int inner = heads * HD;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + SLOTS * SLOT_SMEM);
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + SLOTS * SLOT_BARS);
-  int* xu_lock = reinterpret_cast<int*>(tmem_slot) + 4;                                           // [4], one per scheduler
   AttnItem* table = reinterpret_cast<AttnItem*>(reinterpret_cast<uint8_t*>(tmem_slot) + 64);      // [SLOTS][MAX_ITEMS]
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -161,7 +181,7 @@ attention_tc2_kernel(const __grid_constant__ CUtensorMap tm, __nv_bfloat16* __re
     }
     ptx::fence_barrier_init();
     ptx::prefetch_tensormap(&tm);
-    for (int i = 0; i < 4; ++i) xu_lock[i] = 0;
+    ptx::prefetch_tensormap(&tmkv);
   }
   if (warp == MMA_WARP) ptx::tmem_alloc(tmem_slot, TM_COLS);
   ptx::tc_fence_before();
@@ -201,16 +221,20 @@ attention_tc2_kernel(const __grid_constant__ CUtensorMap tm, __nv_bfloat16* __re
     return c;
   };
 
-  if (warp >= CTRL_WARP0 && ((warp - CTRL_WARP0) & 1) == 0) {
+  // (setmaxnreg sits at the top of each role branch: after a merge point ptxas would apply the smaller budget to all.)
+  if (warp >= CTRL_WARP0 + 2 * SLOTS) {
+    ptx::reg_dealloc<CTRL_REGS>();                  // padding warps of the last control warpgroup: nothing to do
+  } else if (warp >= CTRL_WARP0 && ((warp - CTRL_WARP0) & 1) == 0) {
     // ------------------------------------------------------------------ TMA loader of slot s (blocking waits: a control warp
     // that polls steals issue slots from the softmax warp of its scheduler -- measured: the exp pass of a warp took 1700-2400
     // cycles next to a polling loop against 1280 in isolation)
+    ptx::reg_dealloc<CTRL_REGS>();
     const int s = (warp - CTRL_WARP0) >> 1;
     if (lane == 0) {
       const SlotBars b = slot_bars(bars + s * SLOT_BARS);
       uint8_t* sQ = smem + s * SLOT_SMEM;
-      uint8_t* sK = sQ + Q_BUFS * TILE_BYTES;
-      uint8_t* sV = sK + KV_STAGES * TILE_BYTES;
+      uint8_t* sK = sQ + Q_BUFS * Q_BYTES;
+      uint8_t* sV = sK + KV_STAGES * KV_BYTES;
       // Two cursors over the same (item, key block) sequence: the K stream (which also brings each item's Q tile) runs one
       // block ahead of the V stream.  K(g+1)'s stage frees when QK(g-1) retires, which precedes the retirement of PV(g-2)
       // that frees V(g)'s stage (the MMA thread issues QK(g+1) before PV(g)), so this thread never waits on the later event first.
@@ -218,19 +242,19 @@ attention_tc2_kernel(const __grid_constant__ CUtensorMap tm, __nv_bfloat16* __re
         if (c.j == 0) {
           const int qb = c.n % Q_BUFS;
           if (c.n >= Q_BUFS) ptx::mbar_wait(&b.q_free[qb], ((c.n / Q_BUFS) - 1) & 1);
-          ptx::mbar_arrive_expect_tx(&b.q_full[qb], TILE_BYTES);
-          ptx::tma_load_2d(sQ + qb * TILE_BYTES, &tm, &b.q_full[qb], c.w.head * HD, c.w.seq0 + c.w.q0);
+          ptx::mbar_arrive_expect_tx(&b.q_full[qb], Q_BYTES);
+          ptx::tma_load_2d(sQ + qb * Q_BYTES, &tm, &b.q_full[qb], c.w.head * HD, c.w.seq0 + c.w.q0);
         }
         const int st = c.g % KV_STAGES;
         ptx::mbar_wait(&b.k_empty[st], ((c.g / KV_STAGES) & 1) ^ 1);
-        ptx::mbar_arrive_expect_tx(&b.k_full[st], TILE_BYTES);
-        ptx::tma_load_2d(sK + st * TILE_BYTES, &tm, &b.k_full[st], inner + c.w.head * HD, c.w.seq0 + c.j * BK);
+        ptx::mbar_arrive_expect_tx(&b.k_full[st], KV_BYTES);
+        ptx::tma_load_2d(sK + st * KV_BYTES, &tmkv, &b.k_full[st], inner + c.w.head * HD, c.w.seq0 + c.j * BK);
       };
       auto load_v = [&](const Cursor& c) {
         const int st = c.g % KV_STAGES;
         ptx::mbar_wait(&b.v_empty[st], ((c.g / KV_STAGES) & 1) ^ 1);
-        ptx::mbar_arrive_expect_tx(&b.v_full[st], TILE_BYTES);
-        ptx::tma_load_2d(sV + st * TILE_BYTES, &tm, &b.v_full[st], 2 * inner + c.w.head * HD, c.w.seq0 + c.j * BK);
+        ptx::mbar_arrive_expect_tx(&b.v_full[st], KV_BYTES);
+        ptx::tma_load_2d(sV + st * KV_BYTES, &tmkv, &b.v_full[st], 2 * inner + c.w.head * HD, c.w.seq0 + c.j * BK);
       };
       Cursor kc = first(s);
       Cursor vc = kc;
@@ -246,27 +270,33 @@ attention_tc2_kernel(const __grid_constant__ CUtensorMap tm, __nv_bfloat16* __re
     // All 32 lanes run the loop (identical state in every lane); one elected lane issues.  With the loop inside
     // `if (lane == 0)` the compiler could not prove the operands uniform and emitted a register -> uniform-register
     // conversion loop (ELECT / R2UR.BROADCAST / BRA.U.ANY) in front of every tcgen05.mma: ~100 cycles per MMA.
+    // Two cursors over the slot's flattened (item, key block) sequence: QK^T runs one block ahead of PV ACROSS item
+    // boundaries, so the first S of the next item is already in TMEM when the softmax threads finish the current item
+    // (the first version issued it after the item's last PV: 2400 idle cycles per item in the softmax warps).
+    ptx::reg_dealloc<CTRL_REGS>();
     const int s = (warp - CTRL_WARP0) >> 1;
     const SlotBars b = slot_bars(bars + s * SLOT_BARS);
-    const uint32_t idesc_qk = ptx::make_idesc_bf16(BQ, BK);                       // 128 x 128, A/B K-major
+    const uint32_t idesc_qk = ptx::make_idesc_bf16(BQ, BK);                       // 128 x BK, A/B K-major
     const uint32_t idesc_pv = ptx::make_idesc_bf16(BQ, HD) | (1u << 16);          // 128 x 64, B MN-major
     // descriptor words: hi is the same for every K-major (resp. MN-major) operand, lo = (address & 0x3FFFF) >> 4
     const uint32_t kdesc_hi = (uint32_t)(ptx::make_sw128_kmajor_desc(0) >> 32);
     const uint32_t vdesc_hi = (uint32_t)(make_sw128_mnmajor_desc(0) >> 32);
     const uint32_t a0 = ptx::smem_u32(smem + s * SLOT_SMEM);
     const uint32_t q_lo0 = (uint32_t)ptx::make_sw128_kmajor_desc(a0);
-    const uint32_t k_lo0 = (uint32_t)ptx::make_sw128_kmajor_desc(a0 + TILE_BYTES * Q_BUFS);
-    const uint32_t v_lo0 = (uint32_t)make_sw128_mnmajor_desc(a0 + TILE_BYTES * (Q_BUFS + KV_STAGES));
+    const uint32_t k_lo0 = (uint32_t)ptx::make_sw128_kmajor_desc(a0 + Q_BYTES * Q_BUFS);
+    const uint32_t v_lo0 = (uint32_t)make_sw128_mnmajor_desc(a0 + Q_BYTES * Q_BUFS + KV_BYTES * KV_STAGES);
     const uint32_t tm_s = tmem + s * TM_SLOT;
-    auto issue_qk = [&](uint32_t gg, bool last, uint32_t nn) {
+    auto issue_qk = [&](const Cursor& c) {
+      const uint32_t gg = c.g, nn = c.n;
       const int st = gg % KV_STAGES;
       const int qb = nn % Q_BUFS;
-      const uint32_t q_lo = ptx::bcast0(q_lo0 + qb * (TILE_BYTES >> 4));
+      if (c.j == 0) ptx::mbar_wait(&b.q_full[qb], (nn / Q_BUFS) & 1);
+      const uint32_t q_lo = ptx::bcast0(q_lo0 + qb * (Q_BYTES >> 4));
       ptx::mbar_wait(&b.k_full[st], (gg / KV_STAGES) & 1);
       if (gg > 0) ptx::mbar_wait(b.s_free, (gg - 1) & 1);        // the softmax threads hold S(g-1) in registers
       ptx::tc_fence_after();
-      const uint32_t k_lo = ptx::bcast0(k_lo0 + st * (TILE_BYTES >> 4));
-      const uint32_t lastu = ptx::bcast0(last);
+      const uint32_t k_lo = ptx::bcast0(k_lo0 + st * (KV_BYTES >> 4));
+      const uint32_t lastu = ptx::bcast0(c.j + 1 == c.nblk);
       if (ptx::elect_one()) {
 #pragma unroll
         for (int k = 0; k < HD / 16; ++k)
@@ -277,35 +307,32 @@ attention_tc2_kernel(const __grid_constant__ CUtensorMap tm, __nv_bfloat16* __re
       }
       __syncwarp();
     };
-    uint32_t n = 0, g = 0;
-    for (int k = 0; k < per_slot; ++k) {
-      const AttnItem w = table[s * MAX_ITEMS + k];
-      if (w.len == 0) continue;
-      const int nblk = (w.len + BK - 1) / BK;
-      ptx::mbar_wait(&b.q_full[n % Q_BUFS], (n / Q_BUFS) & 1);
-      issue_qk(g, nblk == 1, n);
-      for (int j = 0; j < nblk; ++j, ++g) {
-        if (j + 1 < nblk) issue_qk(g + 1, j + 2 == nblk, n);
-        const int st = g % KV_STAGES;
-        ptx::mbar_wait(b.p_full, g & 1);                         // P(g) is in TMEM, O has been rescaled
-        if (j == 0 && n > 0) ptx::mbar_wait(b.o_free, (n - 1) & 1);   // previous item's O has been read out
-        ptx::mbar_wait(&b.v_full[st], (g / KV_STAGES) & 1);
-        ptx::tc_fence_after();
-        const uint32_t v_lo = ptx::bcast0(v_lo0 + st * (TILE_BYTES >> 4));
-        const uint32_t acc0 = ptx::bcast0(j != 0);
-        if (ptx::elect_one()) {
+    Cursor qc = first(s);
+    Cursor pc = qc;
+    if (qc.ok) { issue_qk(qc); adv(qc, s); }
+    while (pc.ok) {
+      if (qc.ok) { issue_qk(qc); adv(qc, s); }
+      const uint32_t g = pc.g;
+      const int st = g % KV_STAGES;
+      ptx::mbar_wait(b.p_full, g & 1);                           // P(g) is in TMEM, O has been rescaled
+      if (pc.j == 0 && pc.n > 0) ptx::mbar_wait(b.o_free, (pc.n - 1) & 1);   // previous item's O has been read out
+      ptx::mbar_wait(&b.v_full[st], (g / KV_STAGES) & 1);
+      ptx::tc_fence_after();
+      const uint32_t v_lo = ptx::bcast0(v_lo0 + st * (KV_BYTES >> 4));
+      const uint32_t acc0 = ptx::bcast0(pc.j != 0);
+      if (ptx::elect_one()) {
 #pragma unroll
-          for (int kk = 0; kk < BK / 16; ++kk)
-            ptx::umma_ts_lo(tm_s + TM_O, tm_s + TM_P + kk * 8, v_lo + kk * (2048 >> 4), vdesc_hi, idesc_pv, kk == 0 ? acc0 : 1u);
-          ptx::umma_commit(&b.v_empty[st]);
-          ptx::umma_commit(b.pv_done);
-        }
-        __syncwarp();
+        for (int kk = 0; kk < BK / 16; ++kk)
+          ptx::umma_ts_lo(tm_s + TM_O, tm_s + TM_P + kk * 8, v_lo + kk * (2048 >> 4), vdesc_hi, idesc_pv, kk == 0 ? acc0 : 1u);
+        ptx::umma_commit(&b.v_empty[st]);
+        ptx::umma_commit(b.pv_done);
       }
-      ++n;
+      __syncwarp();
+      adv(pc, s);
     }
   } else {
     // ------------------------------------------------------------------ softmax + output: thread = one query row of a slot
+    ptx::reg_alloc<SOFTMAX_REGS>();
     const int s = warp >> 2;
     const int lane_grp = warp & 3;
     const int row = lane_grp * 32 + lane;
@@ -362,25 +389,25 @@ attention_tc2_kernel(const __grid_constant__ CUtensorMap tm, __nv_bfloat16* __re
         ptx::mbar_wait(b.s_full, g & 1);
         AP(0, t0); t0 = AP_NOW();
         ptx::tc_fence_after();
-        uint32_t raw[4][32];
+        uint32_t raw[CH][32];
 #pragma unroll
-        for (int c = 0; c < 4; ++c) ptx::tmem_ld32_nowait(tbase + TM_S + c * 32, raw[c]);
+        for (int c = 0; c < CH; ++c) ptx::tmem_ld32_nowait(tbase + TM_S + c * 32, raw[c]);
         ptx::tmem_wait_ld();
         ptx::tc_fence_before();
         __syncwarp();
         if (lane == 0) ptx::mbar_arrive(b.s_free);               // S(g) is in registers: QK(g+1) may overwrite it
         AP(1, t0); t0 = AP_NOW();
-        const int nvalid = len - j * BK;                         // valid keys among the block's 128 columns
+        const int nvalid = len - j * BK;                         // valid keys among the block's BK columns
         if (nvalid < BK) {
 #pragma unroll
-          for (int c = 0; c < 4; ++c)
+          for (int c = 0; c < CH; ++c)
 #pragma unroll
             for (int i = 0; i < 32; ++i)
               if (c * 32 + i >= nvalid) raw[c][i] = 0xff800000u;  // -inf
         }
         float mx[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
 #pragma unroll
-        for (int c = 0; c < 4; ++c)
+        for (int c = 0; c < CH; ++c)
 #pragma unroll
           for (int i = 0; i < 32; i += 4) {
             mx[0] = fmaxf(mx[0], __uint_as_float(raw[c][i]));
@@ -400,20 +427,12 @@ attention_tc2_kernel(const __grid_constant__ CUtensorMap tm, __nv_bfloat16* __re
         AP(2, t0); t0 = AP_NOW();
         // exp2 of the whole row into packed bf16 registers FIRST; only the TMEM stores wait for PV(g-1) (which still reads
         // P(g-1)), so that wait is off the critical path.
-        // The exp pass of this warp and that of the other slot's warp on the same scheduler take turns (a lock per
-        // scheduler): the MUFU pipe is the bound of the kernel, and two free-running slots lock IN phase -- both in the exp pass
-        // (MUFU shared, 2 x 1024 cycles) and then both outside it (MUFU idle).  Taking turns puts one slot's load / max /
-        // store / MMA round trip under the other slot's exp pass.
-#if ATTN2_XU_LOCK
-        if (lane == 0) {
-          while (atomicCAS(&xu_lock[lane_grp], 0, 1) != 0) {}
-        }
-        __syncwarp();
-#endif
+        // (Tried and dropped: a per-scheduler lock that makes the slots' exp passes take turns -- the lock hand-over cost more
+        // than the MUFU sharing it avoided.)
         float ls[4] = {0.f, 0.f, 0.f, 0.f};
-        uint32_t pk[4][16];
+        uint32_t pk[CH][16];
 #pragma unroll
-        for (int c = 0; c < 4; ++c) {
+        for (int c = 0; c < CH; ++c) {
 #pragma unroll
           for (int i = 0; i < 32; i += 2) {
             float p0, p1;
@@ -430,17 +449,13 @@ attention_tc2_kernel(const __grid_constant__ CUtensorMap tm, __nv_bfloat16* __re
             pk[c][i >> 1] = pack2(p0, p1);
           }
         }
-#if ATTN2_XU_LOCK
-        __syncwarp();
-        if (lane == 0) atomicExch(&xu_lock[lane_grp], 0);
-#endif
         AP(4, t0); t0 = AP_NOW();
         if (g > 0) ptx::mbar_wait(b.pv_done, (g - 1) & 1);       // PV(g-1) retired: P and O may be touched
         AP(3, t0); t0 = AP_NOW();
         ptx::tc_fence_after();
         if (pending) flush_output();                             // previous item's O (its last PV has just retired)
 #pragma unroll
-        for (int c = 0; c < 4; ++c) ptx::tmem_st16(tbase + TM_P + c * 16, pk[c]);
+        for (int c = 0; c < CH; ++c) ptx::tmem_st16(tbase + TM_P + c * 16, pk[c]);
         l_row = l_row * corr + ((ls[0] + ls[1]) + (ls[2] + ls[3]));
         if (j > 0 && __any_sync(0xffffffffu, need)) {            // rare: some row of this warp moved its offset
           float o[32];
@@ -517,6 +532,12 @@ int launch_attention_tc2(const void* qkv, int ld, void* out, int ldo, const Layo
   CUresult r = fn(&tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(qkv), dims, strides, box, estr,
                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  CUtensorMap tmkv;
+  cuuint32_t boxkv[2] = {64, (cuuint32_t)BK};
+  if (r == CUDA_SUCCESS)
+    r = fn(&tmkv, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(qkv), dims, strides, boxkv, estr,
+           CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+           CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) {
     set_last_error("cuTensorMapEncodeTiled (attention) failed with CUresult " + std::to_string((int)r));
     return CVB_ERR_CUDA;
@@ -532,7 +553,7 @@ int launch_attention_tc2(const void* qkv, int ld, void* out, int ldo, const Layo
   const int want = (n_items + SLOTS - 1) / SLOTS;
   const int grid = want < sms ? want : sms;
   CVB_REQUIRE((n_items + SLOTS * grid - 1) / (SLOTS * grid) <= MAX_ITEMS, "too many query tiles for the per-CTA item table");
-  CVB_CUDA(launch_pdl(attention_tc2_kernel, dim3(grid), dim3(NUM_THREADS), SMEM_BYTES, st, tm,
+  CVB_CUDA(launch_pdl(attention_tc2_kernel, dim3(grid), dim3(NUM_THREADS), SMEM_BYTES, st, tm, tmkv,
                       reinterpret_cast<__nv_bfloat16*>(out), ldo, lay, heads, scale * 1.4426950408889634f, n_items));
   CVB_LAUNCH_CHECK();
   return CVB_OK;

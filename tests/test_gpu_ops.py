@@ -117,6 +117,64 @@ def test_tapgemm_tcgen05_matches_simt(case):
     assert ref.abs().max().item() > 0.1
 
 
+@pytest.mark.parametrize("case", ["linear_256_1536", "linear_1024_256", "conv_k3_320", "conv_k11_d5_128", "convT_s8",
+                                  "final_proj_80", "conv_post_18", "stride8"])
+def test_tapgemm_tcgen05_matches_torch_fp32(case):
+    """The eight tcgen05 shapes against torch itself (F.linear / F.conv1d / F.conv_transpose1d in fp32 on the bf16-rounded
+    weights and inputs, one call per sequence on the un-packed [C, T] tensors): the reference never sees packing.py's
+    tap / phase / segment layout, so a packing bug shared by both engines cannot hide.
+    Tolerance: fp32 accumulation order over K <= 3520 products of bf16 values, 2e-3 of the output scale."""
+    torch.manual_seed(2)
+    lens = [300, 129, 5, 640]
+    bf = torch.bfloat16
+    lay = SeqLayout.build(lens, DEV, halo=32)
+    r = lambda *sh, s=1.0: (torch.randn(*sh) * s).to(bf).float()          # bf16-rounded fp32 master copies
+    kw, cin, n_phase = {}, 256, 1
+    if case == "linear_256_1536":
+        W = r(1536, 256, s=0.06)
+        plan, ref = linear_plan(W, None, bf, DEV), (lambda x: F.linear(x.t(), W).t())
+    elif case == "linear_1024_256":
+        cin, W, b = 1024, r(256, 1024, s=0.03), torch.randn(256)
+        plan, ref = linear_plan(W, b, bf, DEV), (lambda x: F.linear(x.t(), W, b).t())
+    elif case == "conv_k3_320":
+        cin, W, b = 320, r(256, 320, 3, s=0.03), torch.randn(256)
+        plan, ref = conv1d_plan(W, b, bf, DEV), (lambda x: F.conv1d(x[None], W, b, padding=1)[0])
+    elif case == "conv_k11_d5_128":
+        cin, W, b = 128, r(128, 128, 11, s=0.03), torch.randn(128)
+        plan, ref = conv1d_plan(W, b, bf, DEV, dilation=5), (lambda x: F.conv1d(x[None], W, b, padding=25, dilation=5)[0])
+    elif case == "convT_s8":
+        W, b, n_phase = r(256, 128, 16, s=0.03), torch.randn(128), 8
+        plan = conv_transpose1d_plan(W, b, bf, DEV, stride=8, padding=4)
+        ref = lambda x: F.conv_transpose1d(x[None], W, b, stride=8, padding=4)[0]
+    elif case == "final_proj_80":
+        W, b = r(80, 256, s=0.06), torch.randn(80)
+        plan, ref = linear_plan(W, b, bf, DEV), (lambda x: F.linear(x.t(), W, b).t())
+    elif case == "conv_post_18":
+        cin, W, b = 128, r(18, 128, 7, s=0.03), torch.randn(18)
+        plan, ref = conv1d_plan(W, b, bf, DEV), (lambda x: F.conv1d(x[None], W, b, padding=3)[0])
+    else:       # strided analysis conv (source_downs: kernel 16, stride 8, 4 zeros on the left), 18 channels padded to 64
+        cin, W, b = 18, r(256, 18, 16, s=0.1), torch.randn(256)
+        plan = conv1d_plan(W, b, bf, DEV, stride=8, pad_left=4, c_pad=64)
+        ref = lambda x: F.conv1d(F.pad(x, (4, 16))[None], W, b, stride=8)[0]
+    layc = SeqLayout.build(lens, "cpu", halo=32)
+    if case == "stride8":
+        lay_in = layc.derive(8, 1, [l * 8 + 1 for l in lens])
+        xs = [r(cin, l * 8 + 1) for l in lens]
+        A = to_rows(xs, lay_in, 64)
+    else:
+        xs = [r(cin, l) for l in lens]
+        A = to_rows(xs, layc, cin)
+    ncol = 32 if plan.N == 18 else plan.N
+    got = _run_gemm(plan, A.to(DEV).to(bf), lay, ncol, _lib.ENGINE_TCGEN05, **kw).cpu()
+    got = got.reshape(lay.rows, n_phase, ncol)
+    for bi, l in enumerate(lens):
+        want = ref(xs[bi])[:, :l * n_phase]                                     # [N, l * n_phase]
+        have = got[lay.row0[bi]:lay.row0[bi] + l, :, :plan.N].reshape(l * n_phase, plan.N).t()
+        err = (have - want).abs().max().item()
+        assert err < 2e-3 * max(1.0, want.abs().max().item()), (case, bi, err)
+        assert want.abs().max().item() > 0.1
+
+
 def test_tapgemm_epilogue_features_tcgen05():
     """bias + residual + scale + accumulate + dual output (snake) + GroupNorm statistics, bf16 engine vs torch."""
     torch.manual_seed(3)
