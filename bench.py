@@ -123,6 +123,32 @@ def cpu_reference_pass(n_timesteps: int = 10):
     return run
 
 
+def cpu_reference_sweep(n_utt: int, n_timesteps: int = 10):
+    """CPU arm of `--workload sweep`: the first `n_utt` utterances of BASELINE config 5 (the sweep's own seed: generated
+    duration ~ U[2, 30] s after a 3 s prompt), one at a time (the reference asserts B = 1, flow/flow.py:125), through the
+    same oracle port as cpu_reference_pass.  Returns (run_one(u) -> None, audio seconds per utterance)."""
+    from cosyvoice_b200 import synthetic
+    from oracle import encoder_ref, flow_ref, hift_ref
+    fsd, hsd = synthetic.flow_estimator_sd(False, seed=0), synthetic.hift_sd(False, seed=1)
+    esd = synthetic.flow_frontend_sd(False, seed=2)
+    g = torch.Generator().manual_seed(2048)
+    dur = 2.0 + 28.0 * torch.rand(2048, generator=g)
+    n_tok = [int(round(25.0 * float(d))) for d in dur[:n_utt]]
+    gen_frames = [int(n / 25 * SR / 256) for n in n_tok]
+
+    def run_one(u):
+        t, pt, pf, e = synthetic.frontend_inputs(False, n_tok[u], PROMPT_TOKENS, seed=1234 + u, sample_rate=SR)
+        T = PROMPT_FRAMES + gen_frames[u]
+        z = torch.randn(1, 80, T, generator=torch.Generator().manual_seed(4321 + u))
+        with torch.inference_mode():
+            mu, spks, cond, _, _ = encoder_ref.frontend_v1(esd, t, pt, pf, e, sample_rate=SR)
+            mel = flow_ref.solve_euler(fsd, z, flow_ref.cosine_t_span(n_timesteps), mu, torch.ones(1, 1, T), spks, cond)
+            gen = mel[:, :, PROMPT_FRAMES:]
+            pv, nz = hift_ref.draw_source_rng(1, gen.shape[-1] * HOP)
+            hift_ref.hift_inference(hsd, gen, pv, nz)
+    return run_one, [f * HOP / SR for f in gen_frames]
+
+
 def physical_cores() -> int:
     """Physical cores this process may use (SMT siblings do not help the fp32 GEMM/conv kernels of the CPU path)."""
     try:
@@ -183,6 +209,36 @@ def run_reference(args):
         return
     cores = args.threads or physical_cores()
     flush = not args.no_flush_denormal
+    if args.workload == "sweep":
+        # bounded sample of config 5: its first min(--utterances, 16) utterances, each warm-up `--warmup` + median of `--steps`
+        n = min(args.utterances, 16)
+        torch.set_num_threads(cores)
+        torch.set_flush_denormal(flush)
+        run_one, audio = cpu_reference_sweep(n)
+        med = []
+        for u in range(n):
+            for _ in range(args.warmup):
+                run_one(u)
+            ts = []
+            for _ in range(max(args.steps, 1)):
+                t0 = time.perf_counter()
+                run_one(u)
+                ts.append(time.perf_counter() - t0)
+            med.append(statistics.median(ts))
+        val = sum(audio) / sum(med)
+        sample = (f"first {n} utterances of config 5 (generated 2-30 s + 3 s prompt), one at a time (B = 1), front-end + 10 Euler "
+                  f"steps (F.scaled_dot_product_attention) + HiFT, fp32, per utterance {args.warmup} warm-up + median of {args.steps}, "
+                  f"{cores} threads, flush_denormal {'on' if flush else 'off'}")
+        print(json.dumps({
+            "impl": "reference", "metric": "audio_seconds_per_second", "value": val, "unit": "audio-s/s", "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": sum(med) * 1e3, "higher_is_better": True,
+            "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": "BASELINE config 5 (ragged 2-30 s sweep), bounded sample", "sample": sample, "threads": cores,
+                       "audio_seconds": sum(audio), "s_per_utterance": med, "audio_s_per_utterance": audio},
+            "cpu_baseline": {"value": val, "unit": "audio-s/s", "cores": cores, "kind": "port", "sample": sample},
+            "e2e": {"value": val, "unit": "audio-s/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        }))
+        return
     dt, raw = time_cpu_baseline(flush, args.warmup, args.steps, cores)
     val = audio_seconds(1) / dt
     sample = CPU_SAMPLE + f", median of {args.steps} after {args.warmup} warm-up, {cores} threads, flush_denormal {'on' if flush else 'off'}"
@@ -363,9 +419,15 @@ def main():
     ap.add_argument("--threads", type=int, default=0, help="CPU arm: torch threads (default: physical cores)")
     ap.add_argument("--no-flush-denormal", action="store_true", help="CPU arm: leave denormals on")
     ap.add_argument("--no-cpu-baseline", action="store_true", help="B200 arm: skip the cpu_baseline leg (kernel iteration)")
+    ap.add_argument("--workload", default="batch32", choices=["batch32", "sweep"],
+                    help="batch32: BASELINE config 2 (default, the headline); sweep: BASELINE config 5, strong scaling")
+    ap.add_argument("--utterances", type=int, default=2048, help="--workload sweep: utterances in the whole job")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)
+    elif args.workload == "sweep":
+        import bench_sweep
+        bench_sweep.run_sweep(args, sys.modules[__name__])
     else:
         run_ours(args)
 

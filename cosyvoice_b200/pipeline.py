@@ -54,6 +54,46 @@ class AcousticBackend:
         wavs, _ = self.hift.inference_batch(gen, uniform_stride=True)
         return wavs
 
+    @torch.inference_mode()
+    def synthesize_tokens_batches_to_host(self, batches, n_timesteps: int = 10, sample_rate: Optional[int] = None):
+        """A sweep over many batches (the batched replacement of the reference's one-utterance loop,
+        cosyvoice/bin/inference.py:57,79) with the results on the HOST: `batches` yields
+        (tokens, prompt_tokens, prompt_feats, embeddings, zs) lists; returns, per batch, the waveforms [1, L_u] as views of
+        one pinned host buffer.  The device->host copies of batch i run on a side stream into pinned memory while the host
+        packs and enqueues batch i+1, so neither the copy nor the packing sits between two batches on the GPU; the only
+        host wait is at the end.  `self.last_sweep` records the host time spent enqueueing and the time spent waiting."""
+        import time
+        if not hasattr(self, "_d2h_stream"):
+            self._d2h_stream = torch.cuda.Stream(device=self.device)
+        side, main = self._d2h_stream, torch.cuda.current_stream(self.device)
+        out, events = [], []
+        t_host = 0.0
+        t0 = time.perf_counter()
+        for batch in batches:
+            wavs = self.synthesize_tokens_batch(*batch, n_timesteps=n_timesteps, sample_rate=sample_rate)
+            ready = torch.cuda.Event()
+            ready.record(main)
+            sizes = [int(w.shape[-1]) for w in wavs]
+            arena = torch.empty(sum(sizes), dtype=torch.float32, pin_memory=True)
+            views, o = [], 0
+            with torch.cuda.stream(side):
+                side.wait_event(ready)
+                for w, n in zip(wavs, sizes):
+                    v = arena[o:o + n].view(1, n)
+                    v.copy_(w, non_blocking=True)
+                    w.record_stream(side)
+                    views.append(v)
+                    o += n
+                done = torch.cuda.Event()
+                done.record(side)
+            out.append(views)
+            events.append(done)
+        t_host = time.perf_counter() - t0
+        for e in events:
+            e.synchronize()
+        self.last_sweep = dict(host_enqueue_s=t_host, host_wait_s=time.perf_counter() - t0 - t_host, batches=len(out))
+        return out
+
     def prepare_resident_tokens(self, tokens, prompt_tokens, prompt_feats, embeddings, zs, sample_rate: Optional[int] = None):
         """Resident state for step_resident with the front-end inside the step: tokens, prompt mels, speaker vectors and
         noise are copied to HBM here, once."""

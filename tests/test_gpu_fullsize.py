@@ -305,3 +305,33 @@ def test_config5_ragged_subset_members_equal_their_b1_runs_and_the_oracle(monkey
         werr = (wav - want_w).abs().max().item()
         print(f"config 5 member {u} (T = {tot[u]}, {steps} Euler steps) fp32 vs oracle: mel {err:.3e}, waveform {werr:.3e}")
         assert err < 2e-3 and werr < 1e-3, (u, err, werr)
+
+
+def test_sweep_to_host_equals_batch_by_batch_calls():
+    """AcousticBackend.synthesize_tokens_batches_to_host (pinned results, device->host copies on a side stream under the next
+    batch) returns, batch by batch, exactly what synthesize_tokens_batch returns on the device -- also when consecutive
+    batches reuse one HiFT program (same stride bucket), i.e. the copy of batch i is not overtaken by batch i + 1."""
+    from cosyvoice_b200.pipeline import AcousticBackend
+    esd, hsd, fsd = (init_weights.flow_estimator_sd(False, seed=0), init_weights.hift_sd(False, seed=1),
+                     init_weights.flow_frontend_sd(False, seed=2))
+    be = AcousticBackend(esd, hsd, v2=False, dtype=torch.bfloat16, device=DEV, frontend_sd=fsd)
+    n_tok = [[60, 75], [70, 64], [150], [66, 72]]              # batches 0, 1 and 3 share a stride bucket
+
+    def batch(k):
+        cols = [[], [], [], [], []]
+        for i, n in enumerate(n_tok[k]):
+            t, pt, pf, e = init_weights.frontend_inputs(False, n, 25, seed=100 * k + i, sample_rate=SR)
+            T = pf.shape[1] + int(n / 25 * SR / 256)
+            for c, v in zip(cols, (t, pt, pf, e, torch.randn(1, 80, T, generator=torch.Generator().manual_seed(k * 10 + i)))):
+                c.append(v)
+        return tuple(cols)
+    batches = [batch(k) for k in range(len(n_tok))]
+    torch.manual_seed(5)
+    want = [[w.cpu() for w in be.synthesize_tokens_batch(*b, sample_rate=SR)] for b in batches]
+    torch.manual_seed(5)
+    got = be.synthesize_tokens_batches_to_host(iter(batches), sample_rate=SR)
+    assert be.last_sweep["batches"] == len(batches)
+    for k, (g, w) in enumerate(zip(got, want)):
+        assert len(g) == len(w)
+        for a, b in zip(g, w):
+            assert a.is_pinned() and a.shape == b.shape and torch.equal(a, b), k
