@@ -20,7 +20,7 @@ from typing import Dict, List, Optional, Sequence, Tuple
 import torch
 
 from . import _lib, ops
-from .layout import SeqLayout
+from .layout import SeqLayout, copy_async_
 from .packing import TapPlan, build_plan, conv1d_plan, linear_plan
 
 SD = Dict[str, torch.Tensor]
@@ -256,6 +256,25 @@ class _Program:
         self.__dict__.clear()
 
 
+def _stage_to_device(tensors: Sequence[torch.Tensor], device) -> List[torch.Tensor]:
+    """fp32 device copies of a list of tensors; the host ones travel together through one pinned buffer."""
+    host = [i for i, t in enumerate(tensors) if not t.is_cuda]
+    out = [t if not t.is_cuda else t.to(device, torch.float32) for t in tensors]
+    if host:
+        sizes = [tensors[i].numel() for i in host]
+        flat = torch.empty(sum(sizes), dtype=torch.float32, pin_memory=True)
+        o = 0
+        for i, n in zip(host, sizes):
+            flat[o:o + n].copy_(tensors[i].reshape(-1))
+            o += n
+        dev = flat.to(device, non_blocking=True)
+        o = 0
+        for i, n in zip(host, sizes):
+            out[i] = dev[o:o + n].view(tensors[i].shape)
+            o += n
+    return out
+
+
 class _EncoderHandle:
     """`flow.encoder` as the caller sees it: cli/model.py:314 writes `static_chunk_size` on it."""
 
@@ -341,9 +360,12 @@ class _FlowBase:
                 pieces = regulator_segments(int(n_prompt[b]), tok_lens[b] - int(n_prompt[b]), mel_lens[b][0], mel_lens[b][1],
                                             self.input_frame_rate, sample_rate)
                 sg[b, :len(pieces)] = torch.tensor(pieces, dtype=torch.int32)
-        prog.tokens.copy_(tk, non_blocking=True)
-        prog.segs.copy_(sg, non_blocking=True)
-        prog.spk_in.copy_(torch.cat([e.reshape(1, -1) for e in embeddings], 0).to(self.device, torch.float32))
+        copy_async_(prog.tokens, tk)
+        copy_async_(prog.segs, sg)
+        if all(not e.is_cuda for e in embeddings):
+            copy_async_(prog.spk_in, torch.cat([e.reshape(1, -1).float() for e in embeddings], 0))
+        else:
+            prog.spk_in.copy_(torch.cat([e.reshape(1, -1).to(self.device, torch.float32) for e in embeddings], 0))
         prog.run()
         return prog
 
@@ -375,13 +397,18 @@ class _FlowBase:
         st["spks"].copy_(prog.spks)
         st["cond"].zero_()
         st["x"].zero_()
+        # host inputs go up in ONE pinned, non-blocking copy each (see layout.to_device_async): per-utterance copies from
+        # pageable memory would synchronise the stream B times per batch
+        prompt_feats = _stage_to_device(prompt_feats, self.device)
+        if zs is not None:
+            zs = _stage_to_device(zs, self.device)
         for b in range(B):
             r0, (l1, l2) = lay1.row0[b], mel_lens[b]
             if l1:
-                st["cond"][r0:r0 + l1].copy_(prompt_feats[b].reshape(-1, N_FEATS)[:l1].to(self.device, torch.float32))
+                st["cond"][r0:r0 + l1].copy_(prompt_feats[b].reshape(-1, N_FEATS)[:l1])
             T = l1 + l2
             if zs is not None:
-                z = zs[b].reshape(N_FEATS, T).to(self.device, torch.float32)
+                z = zs[b].reshape(N_FEATS, T)
             elif self.V2:
                 z = cfm.rand_noise[0, :, :T].to(self.device)
             else:

@@ -15,7 +15,7 @@ import torch
 from torch.distributions.uniform import Uniform
 
 from . import _lib, ops
-from .layout import SeqLayout
+from .layout import SeqLayout, copy_async_
 from .packing import conv1d_plan, conv_transpose1d_plan, fold_weight_norm, linear_plan
 
 SD = Dict[str, torch.Tensor]
@@ -324,7 +324,7 @@ class B200HiFTGenerator:
         B, L = len(prog.lens), prog.l_cur
         u = Uniform(low=-np.pi, high=np.pi).sample(sample_shape=(B, NB_HARM + 1, 1))
         u[:, 0, :] = 0
-        prog.phase.copy_(u.reshape(B, NB_HARM + 1))
+        copy_async_(prog.phase, u.reshape(B, NB_HARM + 1))          # pinned staging: no stream synchronisation
         prog.noise[:, :, :L].copy_(torch.randn(B, NB_HARM + 1, L, device=self.device))
         torch.randn(B, L, 1, device=self.device)          # consumed and discarded by the reference (:219)
 

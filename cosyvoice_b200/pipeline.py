@@ -61,7 +61,9 @@ class AcousticBackend:
         (tokens, prompt_tokens, prompt_feats, embeddings, zs) lists; returns, per batch, the waveforms [1, L_u] as views of
         one pinned host buffer.  The device->host copies of batch i run on a side stream into pinned memory while the host
         packs and enqueues batch i+1, so neither the copy nor the packing sits between two batches on the GPU; the only
-        host wait is at the end.  `self.last_sweep` records the host time spent enqueueing and the time spent waiting."""
+        host waits are the bounded run-ahead (three batches) and the end.  Host inputs go up through pinned staging
+        (layout.to_device_async), so no copy synchronises the stream.  `self.last_sweep` records the host time spent
+        packing + enqueueing (waits included) and the final wait."""
         import time
         if not hasattr(self, "_d2h_stream"):
             self._d2h_stream = torch.cuda.Stream(device=self.device)
@@ -70,6 +72,8 @@ class AcousticBackend:
         t_host = 0.0
         t0 = time.perf_counter()
         for batch in batches:
+            if len(events) >= 3:
+                events[-3].synchronize()          # bounded run-ahead: at most three batches of results in flight
             wavs = self.synthesize_tokens_batch(*batch, n_timesteps=n_timesteps, sample_rate=sample_rate)
             ready = torch.cuda.Event()
             ready.record(main)
