@@ -57,6 +57,7 @@ SIGNATURES = {
     "cvb200_tapgemm": [C.POINTER(Gemm), _I, _P],
     "cvb200_ffn_fused": [_P, _I, _P, _P, _P, _P, _P, _I, _P, _I, _LAY, _P],
     "cvb200_block_ffn": [_P, _I, _F, _P, _P, _P, _P, _P, _P, _I, _P, _LAY, _P],
+    "cvb200_block_out_ffn": [_P, _I, _P, _I, _P, _P, _F, _P, _P, _P, _P, _P, _P, _I, _P, _LAY, _P],
     "cvb200_split3_bf16": [_P, _I, _I, _I, _P, _I, _L, _P],
     "cvb200_fade_in_out": [_P, _L, _I, _P, _L, _I, _P, _I, _I, _P],
     "cvb200_interp_linear": [_P, _L, _I, _P, _L, _I, _I, _P],

@@ -51,6 +51,8 @@ int launch_ffn_fused(const void*, int, const void*, const float*, const void*, c
                      const cvb200_layout&, cudaStream_t);
 int launch_block_ffn(void*, int, float, const void*, const float*, const float*, const void*, const float*, void*, int, float*,
                      const cvb200_layout&, cudaStream_t);
+int launch_block_out_ffn(void*, int, const void*, int, const void*, const float*, float, const void*, const float*, const float*,
+                         const void*, const float*, void*, int, float*, const cvb200_layout&, cudaStream_t);
 int launch_split3_bf16(const float*, int, int, int, void*, int, long long, cudaStream_t);
 int launch_fade_in_out(float*, long long, int, const float*, long long, int, const double*, int, int, cudaStream_t);
 int launch_interp_linear(const float*, long long, int, float*, long long, int, int, cudaStream_t);
@@ -115,6 +117,13 @@ int cvb200_block_ffn(void* x, int ldx, float eps, const void* w1f, const float* 
                      const float* b2, void* out1, int ldo1, float* stats_out, const cvb200_layout* lay, void* stream) {
   CVB_REQUIRE(lay != nullptr, "null layout");
   return launch_block_ffn(x, ldx, eps, w1f, u1, b1f, w2, b2, out1, ldo1, stats_out, *lay, ST(stream));
+}
+
+int cvb200_block_out_ffn(void* x, int ldx, const void* o, int ldo, const void* wo, const float* bo, float eps, const void* w1f,
+                         const float* u1, const float* b1f, const void* w2, const float* b2, void* out1, int ldo1,
+                         float* stats_out, const cvb200_layout* lay, void* stream) {
+  CVB_REQUIRE(lay != nullptr, "null layout");
+  return launch_block_out_ffn(x, ldx, o, ldo, wo, bo, eps, w1f, u1, b1f, w2, b2, out1, ldo1, stats_out, *lay, ST(stream));
 }
 
 int cvb200_split3_bf16(const float* x, int ldx, int C, int cpad, void* out, int ldo, int64_t rows, void* stream) {

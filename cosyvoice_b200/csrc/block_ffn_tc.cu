@@ -73,7 +73,7 @@ constexpr int BF_TM_H = 0, BF_TM_O = 256, BF_TM_COLS = 512;
 constexpr int BF_BAR_BYTES = 256;
 constexpr int BF_VEC_FLOATS = 2 * BF_H + BF_C;       // b1' | u | b2
 constexpr int BF_XCH_BYTES = 2 * BF_M * 8 + 2 * 2 * BF_M * 8;   // row statistics [tile parity][row] float2 + half-row exchange [use parity][half][row]
-constexpr int BF_SMEM = 1024 + BF_A_BYTES + BF_STAGES * BF_STAGE_BYTES + BF_BAR_BYTES + BF_VEC_FLOATS * 4 + BF_XCH_BYTES;
+constexpr int BF_SMEM = 1024 + BF_A_BYTES + BF_STAGES * BF_STAGE_BYTES + BF_BAR_BYTES + BF_VEC_FLOATS * 4 + BF_XCH_BYTES + BF_C * 4;
 
 #ifdef BF_PROFILE
 #define BF_WAIT(acc, bar, par)             \
@@ -131,9 +131,12 @@ __device__ __forceinline__ void lds128f(uint32_t addr, float (&r)[4]) {
   asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(r[0]), "=f"(r[1]), "=f"(r[2]), "=f"(r[3]) : "r"(addr));
 }
 
+// OUTP: the block's attention out-projection runs first, inside this kernel (see the header comment, "with OUTP").
+template <bool OUTP>
 __global__ void __launch_bounds__(BF_THREADS, 1)
 block_ffn_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CUtensorMap tmW1,
-                 const __grid_constant__ CUtensorMap tmW2, float eps, const float* __restrict__ u1,
+                 const __grid_constant__ CUtensorMap tmW2, const __grid_constant__ CUtensorMap tmO,
+                 const __grid_constant__ CUtensorMap tmWo, const float* __restrict__ bo, float eps, const float* __restrict__ u1,
                  const float* __restrict__ b1, const float* __restrict__ b2, __nv_bfloat16* __restrict__ X, int ldx,
                  __nv_bfloat16* __restrict__ out1, int ldo1, float2* __restrict__ stats_out, const Layout lay, int m_tiles) {
   extern __shared__ uint8_t smem_raw[];
@@ -150,12 +153,14 @@ block_ffn_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
   uint64_t* p_full = h_full + 2;             // [2] bf16 H(c) written back (8 GELU-warp arrivals)
   uint64_t* o_full = p_full + 2;             // the tile's last G2 retired
   uint64_t* o_free = o_full + 1;             // O read out of TMEM by the row warps (4 arrivals)
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(o_free + 1);
+  uint64_t* d0_full = o_free + 1;            // OUTP: the tile's out-projection accumulator is complete in TMEM
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(d0_full + 1);
   float* sb1 = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(bars) + BF_BAR_BYTES);
   float* su1 = sb1 + BF_H;
   float* sb2 = su1 + BF_H;
   float2* srow = reinterpret_cast<float2*>(sb2 + BF_C);          // [2][128] (rstd, -mean rstd) of the tile's rows
   float2* xch = srow + 2 * BF_M;                                 // [2][2][128] partial statistics of half rows
+  float* sbo = reinterpret_cast<float*>(xch + 2 * 2 * BF_M);     // [256] out-projection bias (OUTP)
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   if (threadIdx.x == 0) {
@@ -172,17 +177,25 @@ block_ffn_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
     }
     ptx::mbar_init(o_full, 1);
     ptx::mbar_init(o_free, BF_ROW_WARPS);
+    ptx::mbar_init(d0_full, 1);
     ptx::fence_barrier_init();
     ptx::prefetch_tensormap(&tmX);
     ptx::prefetch_tensormap(&tmW1);
     ptx::prefetch_tensormap(&tmW2);
+    if (OUTP) {
+      ptx::prefetch_tensormap(&tmO);
+      ptx::prefetch_tensormap(&tmWo);
+    }
   }
   if (warp == 1) ptx::tmem_alloc(tmem_slot, BF_TM_COLS);
   for (int i = threadIdx.x; i < BF_H; i += BF_THREADS) {                              // model constants
     sb1[i] = __ldg(b1 + i);
     su1[i] = __ldg(u1 + i);
   }
-  for (int i = threadIdx.x; i < BF_C; i += BF_THREADS) sb2[i] = __ldg(b2 + i);
+  for (int i = threadIdx.x; i < BF_C; i += BF_THREADS) {
+    sb2[i] = __ldg(b2 + i);
+    if (OUTP) sbo[i] = __ldg(bo + i);
+  }
   ptx::tc_fence_before();
   __syncthreads();
   ptx::tc_fence_after();
@@ -229,9 +242,22 @@ block_ffn_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
       // as soon as this tile's last G1 has retired (a_free, committed right after G1(7) is issued), behind the boxes of
       // G2(6): the ring is full at that point, so the wait costs the weight stream nothing, and X lands -- and is
       // normalised -- while GELU(7) / G2(7) run.
+      auto load_g0 = [&](int t) {            // out-projection operands, 8 K steps of 64: W_out[:, 64k, +64) then o[tile, 64k, +64)
+        for (int ks = 0; ks < 512 / BF_BK; ++ks) {
+          ptx::mbar_wait(&w_empty[stage], ph ^ 1);
+          ptx::mbar_arrive_expect_tx(&w_full[stage], BF_STAGE_BYTES);
+          ptx::tma_load_2d(sW + stage * BF_STAGE_BYTES, &tmWo, &w_full[stage], ks * BF_BK, 0);
+          next_stage();
+          ptx::mbar_wait(&w_empty[stage], ph ^ 1);
+          ptx::mbar_arrive_expect_tx(&w_full[stage], BF_STAGE_BYTES / 2);
+          ptx::tma_load_2d(sW + stage * BF_STAGE_BYTES, &tmO, &w_full[stage], ks * BF_BK, t * BF_M);
+          next_stage();
+        }
+      };
       int n = 0;
       load_x(t_first);
       for (int t = t_first; t < m_tiles; t += t_step, ++n) {
+        if (OUTP) load_g0(t);
         load_g1(0);
         for (int c = 0; c < BF_NCH; ++c) {
           if (c + 1 < BF_NCH) load_g1(c + 1);
@@ -281,9 +307,40 @@ block_ffn_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
           next_stage();
         }
       };
+      auto issue_g0 = [&]() {                 // D0 (TMEM columns [0, 256) = H0 | H1) = o . W_out^T, K = 512
+        for (int ks = 0; ks < 512 / BF_BK; ++ks) {
+          BF_WAIT(prof[4], &w_full[stage], ph);
+          const int st_w = stage;
+          next_stage();
+          BF_WAIT(prof[4], &w_full[stage], ph);
+          const int st_o = stage;
+          next_stage();
+          ptx::tc_fence_after();
+          const uint32_t wo_lo = ptx::bcast0(w_lo0 + st_w * (BF_STAGE_BYTES >> 4));
+          const uint32_t o_lo = ptx::bcast0(w_lo0 + st_o * (BF_STAGE_BYTES >> 4));
+          const uint32_t first = ptx::bcast0(ks == 0), last = ptx::bcast0(ks + 1 == 512 / BF_BK);
+          if (ptx::elect_one()) {
+#pragma unroll
+            for (int kk = 0; kk < 4; ++kk)
+              ptx::umma_ss_lo(tmem + BF_TM_H, o_lo + kk * 2, desc_hi, wo_lo + kk * 2, desc_hi, idesc2, (kk == 0 && first) ? 0u : 1u);
+            ptx::umma_commit(&w_empty[st_w]);
+            ptx::umma_commit(&w_empty[st_o]);
+            if (last) ptx::umma_commit(d0_full);
+          }
+          __syncwarp();
+        }
+      };
       int n = 0;
       for (int t = t_first; t < m_tiles; t += t_step, ++n) {
-        BF_WAIT(prof[0], a_full, n & 1);          // the raw tile is the operand: nothing sits between the load and G1(0)
+        if (OUTP) {
+          // the accumulator shares H0 | H1 with the GELU outputs the previous tile's last G2 still reads
+          if (n > 0) BF_WAIT(prof[0], o_full, (n - 1) & 1);
+          ptx::tc_fence_after();
+          issue_g0();
+          BF_WAIT(prof[0], st_full, n & 1);       // the row warps have turned D0 into the bf16 X tile in shared memory
+        } else {
+          BF_WAIT(prof[0], a_full, n & 1);        // the raw tile is the operand: nothing sits between the load and G1(0)
+        }
         ptx::tc_fence_after();
         issue_g1(0, false);
         for (int c = 0; c < BF_NCH; ++c) {
@@ -442,18 +499,68 @@ block_ffn_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
 
     constexpr int NG = BF_ROW_COLS / 32;       // 32-column groups per thread
     int n = 0;
-    stats_tile(0);
+    if (!OUTP) stats_tile(0);
+    const uint32_t sbo_addr = ptx::smem_u32(sbo) + c0 * 4;
     for (int t = t_first; t < m_tiles; t += t_step, ++n) {
-      // ---- the next tile's row statistics first: the GELU warps need them at its chunk 0
-      if (t + t_step < m_tiles) stats_tile(n + 1);
-
-      // ---- drain: O + b2 + X -> X (bf16) in 32-column groups; the residual (L2-resident: the TMA read it a tile ago) is
-      // requested two groups ahead, the first two before the wait on the last GEMM
       const int row = t * BF_M + trow;
       const int b = __ldg(lay.tile_seq + t);
       const bool valid = __ldg(lay.tile_row0 + t) + trow < __ldg(lay.seq_len + b);
       __nv_bfloat16* xr = X + (size_t)row * ldx + c0;
       uint32_t res[2][2][8];                   // [group parity][16-column half][8 packed pairs]
+      if constexpr (OUTP) {
+        // ---- out-projection epilogue: X' = bf16((D0 + b_out) + X_old), written over the X_old tile in shared memory (the
+        // A operand of every G1 of this tile) and to X in global memory (L2), where this thread reads it back as the residual
+        // of the drain below (keeping it in 64 registers spilled), plus its LayerNorm statistics.  Same arithmetic, in the
+        // same order, as the separate out-projection GEMM's epilogue.
+        BF_WAIT(prof[5], a_full, n & 1);
+        BF_WAIT(prof[5], d0_full, n & 1);
+        ptx::tc_fence_after();
+        BF_T0();
+        float2 s = f2(0.f), ss = f2(0.f);
+        float pivot = 0.f;
+#pragma unroll
+        for (int k = 0; k < NG; ++k) {
+          float v[32];
+          ptx::tmem_ld32(tbase + BF_TM_H + c0 + k * 32, v);
+          const uint32_t slab = a_row + (k >> 1) * 16384;
+#pragma unroll
+          for (int jj = 0; jj < 4; ++jj) {
+            const uint32_t addr = slab + (((((k & 1) << 2) + jj) ^ swz) << 4);     // 16-byte chunk = 8 columns of the 64-wide slab
+            uint32_t r[4], y[4];
+            float bb[8];
+            lds128(addr, r);
+            lds128f(sbo_addr + (k * 32 + jj * 8) * 4, reinterpret_cast<float(&)[4]>(bb[0]));
+            lds128f(sbo_addr + (k * 32 + jj * 8 + 4) * 4, reinterpret_cast<float(&)[4]>(bb[4]));
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+              const float2 yv = __fadd2_rn(__fadd2_rn(make_float2(v[jj * 8 + 2 * e], v[jj * 8 + 2 * e + 1]),
+                                                      make_float2(bb[2 * e], bb[2 * e + 1])), unpack_bf16x2(r[e]));
+              y[e] = valid ? pack_bf16x2(yv.x, yv.y) : 0u;
+            }
+            if (k == 0 && jj == 0) pivot = unpack_bf16x2(y[0]).x;
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+              const float2 d = __fadd2_rn(unpack_bf16x2(y[e]), f2(-pivot));
+              s = __fadd2_rn(s, d);
+              ss = __ffma2_rn(d, d, ss);
+            }
+            sts128(addr, y);
+            *reinterpret_cast<uint4*>(xr + k * 32 + jj * 8) = make_uint4(y[0], y[1], y[2], y[3]);
+          }
+        }
+        const float2 st = finish(pivot, s, ss);
+        if (hf == 0) srow[(n & 1) * BF_M + trow] = st;
+        ptx::fence_proxy_async();              // the tile was written by threads, the MMA reads it through the async proxy
+        ptx::tc_fence_before();                // D0 is in registers: G1(0) may overwrite H0
+        __syncwarp();
+        if (lane == 0) ptx::mbar_arrive(st_full);
+        BF_T1(prof[6]);
+      } else {
+        // ---- the next tile's row statistics first: the GELU warps need them at its chunk 0
+        if (t + t_step < m_tiles) stats_tile(n + 1);
+      }
+      // ---- drain: O + b2 + X -> X (bf16) in 32-column groups; the residual (L2-resident: the TMA read it a tile ago, or
+      // this thread has just written it) is requested two groups ahead, the first two before the wait on the last GEMM
 #pragma unroll
       for (int k = 0; k < 2; ++k) {
         ldg256(xr + k * 32, res[k][0]);
@@ -482,10 +589,12 @@ block_ffn_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
           for (int i = 0; i < 16; i += 4) {
             float bb[4];
             lds128f(sb2_addr + (k * 32 + g16 * 16 + i) * 4, bb);
+            const uint32_t r0 = res[k & 1][g16][i >> 1];
+            const uint32_t r1 = res[k & 1][g16][(i >> 1) + 1];
             const float2 y0 = __fadd2_rn(__fadd2_rn(make_float2(v[g16 * 16 + i], v[g16 * 16 + i + 1]), make_float2(bb[0], bb[1])),
-                                         unpack_bf16x2(res[k & 1][g16][i >> 1]));
+                                         unpack_bf16x2(r0));
             const float2 y1 = __fadd2_rn(__fadd2_rn(make_float2(v[g16 * 16 + i + 2], v[g16 * 16 + i + 3]), make_float2(bb[2], bb[3])),
-                                         unpack_bf16x2(res[k & 1][g16][(i >> 1) + 1]));
+                                         unpack_bf16x2(r1));
             y[i >> 1] = valid ? pack_bf16x2(y0.x, y0.y) : 0u;
             y[(i >> 1) + 1] = valid ? pack_bf16x2(y1.x, y1.y) : 0u;
           }
@@ -528,32 +637,64 @@ block_ffn_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant_
 
 }  // namespace
 
-int launch_block_ffn(void* x, int ldx, float eps, const void* w1f, const float* u1, const float* b1f, const void* w2,
-                     const float* b2, void* out1, int ldo1, float* stats_out, const Layout& lay, cudaStream_t st) {
+// o / wo / bo == nullptr: norm3 + FeedForward + residual only (cvb200_block_ffn); otherwise the attention out-projection of the
+// block runs first inside the same kernel (cvb200_block_out_ffn).
+static int launch_block_ffn_impl(void* x, int ldx, const void* o, int ldo, const void* wo, const float* bo, float eps,
+                                 const void* w1f, const float* u1, const float* b1f, const void* w2, const float* b2, void* out1,
+                                 int ldo1, float* stats_out, const Layout& lay, cudaStream_t st) {
   CVB_REQUIRE(x && w1f && u1 && b1f && w2 && b2, "null operand");
   CVB_REQUIRE(lay.rows > 0 && lay.rows % BF_M == 0, "rows must be a positive multiple of 128");
   CVB_REQUIRE(ldx >= BF_C && ldx % 16 == 0 && (reinterpret_cast<uintptr_t>(x) & 31) == 0,
               "the residual stream must be 32-byte aligned with a 32-byte row pitch");
   CVB_REQUIRE(!out1 || (ldo1 >= BF_C && ldo1 % 16 == 0 && (reinterpret_cast<uintptr_t>(out1) & 31) == 0), "out1 alignment");
   CVB_REQUIRE((reinterpret_cast<uintptr_t>(stats_out) & 7) == 0, "stats_out must be 8-byte aligned");
+  const bool outp = o != nullptr;
+  CVB_REQUIRE(!outp || (wo && bo && ldo >= 512 && ldo % 8 == 0 && (reinterpret_cast<uintptr_t>(o) & 15) == 0),
+              "out-projection operands: o bf16 [rows, ldo >= 512] 16-byte aligned, W_out [256, 512], b_out [256]");
   static std::once_flag once;
   static cudaError_t attr_err = cudaSuccess;
   std::call_once(once, [] {
-    attr_err = cudaFuncSetAttribute(block_ffn_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, BF_SMEM);
+    attr_err = cudaFuncSetAttribute(block_ffn_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, BF_SMEM);
+    if (attr_err == cudaSuccess)
+      attr_err = cudaFuncSetAttribute(block_ffn_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, BF_SMEM);
   });
   CVB_CUDA(attr_err);
-  CUtensorMap tmX, tmW1, tmW2;
+  CUtensorMap tmX, tmW1, tmW2, tmO, tmWo;
   CVB_TRY(make_map_2d_bf16(&tmX, x, BF_C, (uint64_t)lay.rows, (uint64_t)ldx, BF_BK, BF_M));
   CVB_TRY(make_map_2d_bf16(&tmW1, w1f, BF_C, BF_H, BF_C, BF_BK, BF_CH));
   CVB_TRY(make_map_2d_bf16(&tmW2, w2, BF_H, BF_C, BF_H, BF_BK, BF_C));
+  if (outp) {
+    CVB_TRY(make_map_2d_bf16(&tmO, o, 512, (uint64_t)lay.rows, (uint64_t)ldo, BF_BK, BF_M));
+    CVB_TRY(make_map_2d_bf16(&tmWo, wo, 512, BF_C, 512, BF_BK, BF_C));
+  } else {
+    tmO = tmX;
+    tmWo = tmX;
+  }
   const int m_tiles = lay.rows / BF_M;
   const int sms = device_sm_count();
   const int grid = m_tiles < sms ? m_tiles : sms;
-  CVB_CUDA(launch_pdl(block_ffn_kernel, dim3(grid), dim3(BF_THREADS), BF_SMEM, st, tmX, tmW1, tmW2, eps, u1, b1f, b2,
-                      reinterpret_cast<__nv_bfloat16*>(x), ldx, reinterpret_cast<__nv_bfloat16*>(out1), ldo1,
-                      reinterpret_cast<float2*>(stats_out), lay, m_tiles));
+  if (outp)
+    CVB_CUDA(launch_pdl(block_ffn_kernel<true>, dim3(grid), dim3(BF_THREADS), BF_SMEM, st, tmX, tmW1, tmW2, tmO, tmWo, bo, eps, u1,
+                        b1f, b2, reinterpret_cast<__nv_bfloat16*>(x), ldx, reinterpret_cast<__nv_bfloat16*>(out1), ldo1,
+                        reinterpret_cast<float2*>(stats_out), lay, m_tiles));
+  else
+    CVB_CUDA(launch_pdl(block_ffn_kernel<false>, dim3(grid), dim3(BF_THREADS), BF_SMEM, st, tmX, tmW1, tmW2, tmO, tmWo, bo, eps, u1,
+                        b1f, b2, reinterpret_cast<__nv_bfloat16*>(x), ldx, reinterpret_cast<__nv_bfloat16*>(out1), ldo1,
+                        reinterpret_cast<float2*>(stats_out), lay, m_tiles));
   CVB_LAUNCH_CHECK();
   return CVB_OK;
+}
+
+int launch_block_ffn(void* x, int ldx, float eps, const void* w1f, const float* u1, const float* b1f, const void* w2,
+                     const float* b2, void* out1, int ldo1, float* stats_out, const Layout& lay, cudaStream_t st) {
+  return launch_block_ffn_impl(x, ldx, nullptr, 0, nullptr, nullptr, eps, w1f, u1, b1f, w2, b2, out1, ldo1, stats_out, lay, st);
+}
+
+int launch_block_out_ffn(void* x, int ldx, const void* o, int ldo, const void* wo, const float* bo, float eps, const void* w1f,
+                         const float* u1, const float* b1f, const void* w2, const float* b2, void* out1, int ldo1,
+                         float* stats_out, const Layout& lay, cudaStream_t st) {
+  CVB_REQUIRE(o && wo && bo, "null out-projection operand");
+  return launch_block_ffn_impl(x, ldx, o, ldo, wo, bo, eps, w1f, u1, b1f, w2, b2, out1, ldo1, stats_out, lay, st);
 }
 
 }  // namespace cvb

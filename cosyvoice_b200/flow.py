@@ -52,7 +52,9 @@ class _Weights:
         dev = lambda t, dt: t.detach().to(device=device, dtype=dt).contiguous()
         w1f, u1, b1f = ops.fold_layernorm(w1.to(device), sd[p + "ff.net.0.proj.bias"], sd[p + "norm3.weight"],
                                           sd[p + "norm3.bias"], torch.bfloat16)
-        return (w1f, u1, b1f, dev(w2, torch.bfloat16), dev(sd[p + "ff.net.2.bias"], torch.float32))
+        wo, bo = sd[p + "attn1.to_out.0.weight"], sd[p + "attn1.to_out.0.bias"]
+        outp = (dev(wo, torch.bfloat16), dev(bo, torch.float32)) if tuple(wo.shape) == (256, 512) else None
+        return (w1f, u1, b1f, dev(w2, torch.bfloat16), dev(sd[p + "ff.net.2.bias"], torch.float32), outp)
 
     def __init__(self, sd: SD, causal: bool, dtype: torch.dtype, device):
         self.causal, self.dtype, self.device = causal, dtype, device
@@ -146,6 +148,12 @@ class _Program:
             raise ValueError(f"CVB200_FUSED_FFN must be auto, 0 or 1 (got {mode!r})")
         self.fused_ffn = engine == _lib.ENGINE_TCGEN05 and mode != "0"
         self.fused_ffn_min_tiles = FUSED_FFN_MIN_TILES if mode == "auto" else 1
+        # CVB200_FUSED_OUT=1: the attention out-projection as the first GEMM of the same kernel (cvb200_block_out_ffn).  The two
+        # forms are bit-identical (tests/test_gpu_ops.py); measured on the bench workload the fused form is NOT faster (block_ffn
+        # 43.9 -> 62.4 ms per step, tap GEMM 111.0 -> 91.7 ms, step 252.5 -> 255.0 ms): every CTA already streams the block's
+        # 1 MB of FFN weights per 128-row tile from L2 (~10 TB/s over 148 SMs) and the out-projection adds 384 KB per tile to
+        # that stream, so it stays off by default.
+        self.fused_out = os.environ.get("CVB200_FUSED_OUT", "0") == "1"
         R, S = lay.rows, lay.n_seq
         z = lambda *shape, dtype=dt: torch.zeros(*shape, dtype=dtype, device=dev)
         self.t = z(S, dtype=torch.float32)
@@ -288,14 +296,21 @@ class _Program:
             fl = sum(4 * HEADS * HEAD_DIM * l * l for l in L.lens)
             self.ops.append(ops.attention_op(qkv, o, L, HEADS, HEAD_DIM ** -0.5, flops=fl))
             self.flops += fl
-            self._gemm(t["out"], o, L, X, res=X)
             if fuse:
+                # to_out + residual, norm3, FeedForward, residual (+ the next block's norm1 statistics): one kernel
+                w1f, u1, b1f, w2, b2, outp = t["ffw"]
                 fl = (t["ff1"].flops_per_row + t["ff2"].flops_per_row) * sum(L.lens)
-                w1f, u1, b1f, w2, b2 = t["ffw"]
+                kw = {}
+                if outp is not None and self.fused_out:
+                    fl += t["out"].flops_per_row * sum(L.lens)
+                    kw = dict(attn_out=o, w_out=outp[0], b_out=outp[1])
+                else:
+                    self._gemm(t["out"], o, L, X, res=X)
                 self.ops.append(ops.block_ffn_op(X, w1f, u1, b1f, w2, b2, L, flops=fl, out1=last_copy if last else None,
-                                                 stats_out=None if last else stats))
+                                                 stats_out=None if last else stats, **kw))
                 self.flops += fl
                 continue
+            self._gemm(t["out"], o, L, X, res=X)
             self.ops.append(ops.layernorm_op(X, n, t["ln3"][0], t["ln3"][1], R))
             self._gemm(t["ff1"], n, L, f, act=_lib.ACT_GELU)
             if last:

@@ -204,7 +204,8 @@ def fold_layernorm(w: torch.Tensor, b: Optional[torch.Tensor], gamma: torch.Tens
 
 def block_ffn_op(x: torch.Tensor, w1f: torch.Tensor, u1: torch.Tensor, b1f: torch.Tensor, w2: torch.Tensor, b2: torch.Tensor,
                  lay: SeqLayout, out1: Optional[torch.Tensor] = None, stats_out: Optional[torch.Tensor] = None,
-                 eps: float = 1e-5, flops: int = 0) -> Op:
+                 eps: float = 1e-5, flops: int = 0, attn_out: Optional[torch.Tensor] = None,
+                 w_out: Optional[torch.Tensor] = None, b_out: Optional[torch.Tensor] = None) -> Op:
     """x += W2 . gelu(W1 . LN(x) + b1) + b2 on the bf16 residual stream in one tcgen05 kernel, LayerNorm folded into
     (w1f, u1, b1f) by fold_layernorm; optionally stats_out[row] = (rstd, -mean rstd) of the new rows
     (include/cvb200.h cvb200_block_ffn)."""
@@ -217,9 +218,21 @@ def block_ffn_op(x: torch.Tensor, w1f: torch.Tensor, u1: torch.Tensor, b1f: torc
                                  and stats_out.shape[0] >= lay.rows and stats_out.shape[-1] == 2)
     lib = _lib.load()
     layc = lay.c
-    args = (x.data_ptr(), x.stride(0), eps, w1f.data_ptr(), u1.data_ptr(), b1f.data_ptr(), w2.data_ptr(), b2.data_ptr(),
+    tail = (eps, w1f.data_ptr(), u1.data_ptr(), b1f.data_ptr(), w2.data_ptr(), b2.data_ptr(),
             _ptr(out1), out1.stride(0) if out1 is not None else 0, _ptr(stats_out), C.byref(layc))
-    keep = (x, w1f, u1, b1f, w2, b2, out1, stats_out, lay, layc)
+    keep = (x, w1f, u1, b1f, w2, b2, out1, stats_out, lay, layc, attn_out, w_out, b_out)
+    if attn_out is not None:
+        # the attention out-projection + residual add of the block runs first, inside the same kernel (cvb200_block_out_ffn)
+        _require_cuda(attn_out, w_out, b_out)
+        assert attn_out.dtype == torch.bfloat16 and attn_out.stride(1) == 1 and attn_out.shape[1] >= 512
+        assert w_out.dtype == torch.bfloat16 and tuple(w_out.shape) == (256, 512) and w_out.is_contiguous()
+        assert b_out.dtype == torch.float32 and b_out.numel() == 256 and b_out.is_contiguous()
+        args = (x.data_ptr(), x.stride(0), attn_out.data_ptr(), attn_out.stride(0), w_out.data_ptr(), b_out.data_ptr()) + tail
+
+        def launch(_keep=keep):
+            _lib.check(lib.cvb200_block_out_ffn(*args, _stream()), "block_out_ffn")
+        return _profiled("block_ffn", flops, launch)
+    args = (x.data_ptr(), x.stride(0)) + tail
 
     def launch(_keep=keep):
         _lib.check(lib.cvb200_block_ffn(*args, _stream()), "block_ffn")

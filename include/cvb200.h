@@ -163,6 +163,18 @@ int cvb200_ffn_fused(const void* a, int lda, const void* w1, const float* b1, co
 int cvb200_block_ffn(void* x, int ldx, float eps, const void* w1f, const float* u1, const float* b1f, const void* w2,
                      const float* b2, void* out1, int ldo1, float* stats_out, const cvb200_layout* lay, void* stream);
 
+/* The same with the block's attention out-projection in front, still one kernel (csrc/block_ffn_tc.cu, OUTP):
+ *   x  = bf16((o . W_out^T + b_out) + x)                      attn1's to_out[0] + residual add,
+ *                                                             cosyvoice/flow/components/transformer.py:266-276 (diffusers
+ *                                                             Attention.to_out[0], `hidden_states = attn_output + hidden_states`)
+ *   x += W2 . gelu(W1 . LayerNorm(x; g3, be3) + b1) + b2      as cvb200_block_ffn
+ * o: the attention output, bf16 [rows, ldo >= 512] (heads concatenated); wo: bf16 [256, 512] (nn.Linear layout); bo [256] fp32.
+ * The intermediate x is rounded to bf16 exactly as the separate out-projection GEMM (cvb200_tapgemm with a RES_ACT residual)
+ * writes it, lives only in shared memory / registers, and the two forms give bit-identical results. */
+int cvb200_block_out_ffn(void* x, int ldx, const void* o, int ldo, const void* wo, const float* bo, float eps, const void* w1f,
+                         const float* u1, const float* b1f, const void* w2, const float* b2, void* out1, int ldo1,
+                         float* stats_out, const cvb200_layout* lay, void* stream);
+
 /* fp32 -> three bf16 operands with x = x1 + x2 + x3 (24 mantissa bits): out[row, i*cpad + c] = x_i[row, c], i = 0..2.
  * Lets the f0 predictor (cosyvoice/hifigan/f0_predictor.py:52-55, whose output is integrated into the source phase)
  * run on the bf16 tensor cores with split operands: one tap GEMM over the cross terms x_i * w_k of lowest order. */

@@ -518,6 +518,63 @@ def test_block_ffn_matches_torch(lens):
     assert torch.equal(x2, x)
 
 
+@pytest.mark.parametrize("lens", [[200, 77], [128], [1000, 3, 640, 129], [609] * 40])
+def test_block_out_ffn_equals_out_projection_then_block_ffn(lens):
+    """cvb200_block_out_ffn (attention out-projection + residual + norm3 + FeedForward + residual in ONE kernel) against the two
+    launches it replaces -- cvb200_tapgemm (out-projection, bias, bf16 residual) then cvb200_block_ffn: BIT-identical stream,
+    copy and statistics (same K order in the accumulator, same epilogue arithmetic) -- and against torch on the same
+    bf16-rounded operands.  Rows past the valid lengths come out as zeros."""
+    torch.manual_seed(43)
+    lay = SeqLayout.build(lens, DEV)
+    R = lay.rows
+    x0 = torch.zeros(R, 256, device=DEV)
+    o = torch.zeros(R, 512, device=DEV)
+    for b, l in enumerate(lens):
+        x0[lay.row0[b]:lay.row0[b] + l] = torch.randn(l, 256, device=DEV) * 1.5 + 3 * torch.randn(l, 1, device=DEV)
+        o[lay.row0[b]:lay.row0[b] + l] = torch.randn(l, 512, device=DEV)
+    o[lay.row0[0] + lens[0]:lay.row0[0] + lay.strides[0]] = 5.0          # garbage in pad rows of the attention output must not leak
+    x0, o = x0.to(torch.bfloat16), o.to(torch.bfloat16)
+    wo = (torch.randn(256, 512, device=DEV) * (1.0 / 512) ** 0.5).to(torch.bfloat16)
+    bo = torch.randn(256, device=DEV) * 0.1
+    w1 = torch.randn(1024, 256, device=DEV) * (2.0 / 256) ** 0.5
+    w2 = (torch.randn(256, 1024, device=DEV) * (2.0 / 1024) ** 0.5).to(torch.bfloat16)
+    b1, b2 = torch.randn(1024, device=DEV) * 0.1, torch.randn(256, device=DEV) * 0.1
+    g3, be3 = 1 + 0.2 * torch.randn(256, device=DEV), 0.1 * torch.randn(256, device=DEV)
+    w1f, u1, b1f = ops.fold_layernorm(w1, b1, g3, be3, torch.bfloat16)
+    # the two-launch form
+    plan = linear_plan(wo.float(), bo, torch.bfloat16, DEV)
+    xa = x0.clone()
+    ops.gemm_op(plan, o, lay, xa, engine=_lib.ENGINE_TCGEN05, res=xa)()
+    x_mid = xa.clone()
+    out1a, sta = torch.full((R, 256), 7.0, device=DEV, dtype=torch.bfloat16), torch.full((R, 2), 7.0, device=DEV)
+    ops.block_ffn_op(xa, w1f, u1, b1f, w2, b2, lay, out1=out1a, stats_out=sta)()
+    # the fused form
+    xb = x0.clone()
+    out1b, stb = torch.full((R, 256), 7.0, device=DEV, dtype=torch.bfloat16), torch.full((R, 2), 7.0, device=DEV)
+    ops.block_ffn_op(xb, w1f, u1, b1f, w2, b2, lay, out1=out1b, stats_out=stb, attn_out=o, w_out=wo, b_out=bo)()
+    _sync()
+    assert torch.equal(xb, xa) and torch.equal(out1b, out1a) and torch.equal(stb, sta)
+    # torch on the same operands
+    F = torch.nn.functional
+    mid = (x0.float() + o.float() @ wo.float().t() + bo).to(torch.bfloat16).float()
+    for b, l in enumerate(lens):
+        r0 = lay.row0[b]
+        assert (x_mid[r0:r0 + l].float() - mid[r0:r0 + l]).abs().max().item() < 2e-2 * max(1.0, mid[r0:r0 + l].abs().max().item())
+    h = F.gelu(F.layer_norm(mid, (256,)) @ w1f.float().t() + b1f).to(torch.bfloat16).float()
+    want = mid + h @ w2.float().t() + b2
+    for b, l in enumerate(lens):
+        r0 = lay.row0[b]
+        err = (xb[r0:r0 + l].float() - want[r0:r0 + l]).abs().max().item()
+        assert err < 3e-2 * max(1.0, want[r0:r0 + l].abs().max().item()), (b, l, err)
+        for buf in (xb, out1b, stb):
+            assert buf[r0 + l:r0 + lay.strides[b]].float().abs().max().item() == 0
+    # second launch without the optional outputs on the same buffers (barrier phases, TMEM reuse)
+    xc = x0.clone()
+    ops.block_ffn_op(xc, w1f, u1, b1f, w2, b2, lay, attn_out=o, w_out=wo, b_out=bo)()
+    _sync()
+    assert torch.equal(xc, xb)
+
+
 def test_folded_layernorm_projection_matches_layernorm_then_projection():
     """epilogue.row_stats: the QKV projection reading the RAW bf16 stream with norm1 folded into its weights (statistics
     from cvb200_block_ffn's side output) against LayerNorm -> bf16 -> projection on the same engine, and against torch."""
