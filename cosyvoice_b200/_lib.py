@@ -28,6 +28,7 @@ class Epilogue(C.Structure):
         ("ldo0", C.c_int32), ("out0_dt", C.c_int32), ("phase_col", C.c_int32), ("out1_mode", C.c_int32),
         ("ldo1", C.c_int32), ("out1_dt", C.c_int32), ("out1_slope", C.c_float), ("gn_groups", C.c_int32),
         ("row_stats", C.c_void_p), ("row_u", C.c_void_p),
+        ("row_parts", C.c_void_p), ("row_parts_out", C.c_void_p), ("row_eps", C.c_float), ("reserved0", C.c_int32),
     ]
 
 

@@ -74,8 +74,8 @@ int launch_l2_normalize(const float*, float*, int, int, cudaStream_t);
 
 using namespace cvb;
 // the ctypes mirror in cosyvoice_b200/_lib.py relies on this layout (tests/test_lib_cpu.py)
-static_assert(sizeof(cvb200_epilogue) == 144, "cvb200_epilogue layout");
-static_assert(sizeof(cvb200_gemm) == 368, "cvb200_gemm layout");
+static_assert(sizeof(cvb200_epilogue) == 168, "cvb200_epilogue layout");
+static_assert(sizeof(cvb200_gemm) == 392, "cvb200_gemm layout");
 static_assert(sizeof(cvb200_layout) == 48, "cvb200_layout layout");
 #define ST(s) reinterpret_cast<cudaStream_t>(s)
 #define NEED(p, what)                                                                    \

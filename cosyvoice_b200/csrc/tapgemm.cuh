@@ -198,11 +198,29 @@ __device__ __forceinline__ void snake_vec(const float* __restrict__ alpha, const
 // Applies the epilogue to the NV consecutive columns [n0, n0+NV) of output row m (phase `phase`) and stores them.
 //   b: sequence of the row, valid: row (and phase) inside the sequence's valid length.
 // GroupNorm partial sums of this chunk are ADDED to (gsum, gsq).
-template <int NV, bool PRECISE>
+// RP: the row-partials variant (row_parts / row_parts_out of include/cvb200.h).  A separate instantiation of the tcgen05
+// kernel, so that the common GEMMs do not carry its code (the epilogue sits close to the instruction-cache limit).
+template <int NV, bool PRECISE, bool RP = false>
 __device__ __forceinline__ void epi_apply(const Epi& e, size_t m, int b, bool valid, int phase, int n0, float (&v)[NV],
                                           float& gsum, float& gsq) {
   static_assert(NV % 4 == 0, "chunk must be a multiple of 4 columns");
-  if (e.row_stats) {                   // folded LayerNorm: per-row scale and rank-1 mean correction (include/cvb200.h)
+  if (RP && e.row_parts) {             // folded LayerNorm from the producer's partial sums (8 x (sum, sum of squares) per row)
+    const float4* pp = reinterpret_cast<const float4*>(e.row_parts + m * 16);
+    float sx = 0.f, sq = 0.f;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const float4 t = __ldg(pp + i);
+      sx += t.x + t.z;
+      sq += t.y + t.w;
+    }
+    const float mean = sx * (1.f / 256.f);
+    const float rstd = rsqrtf(fmaxf(sq * (1.f / 256.f) - mean * mean, 0.f) + e.row_eps);
+    const float nb = -mean * rstd;
+    float u[NV];
+    vec_load_f32<NV>(e.row_u + n0, u);
+#pragma unroll
+    for (int j = 0; j < NV; ++j) v[j] = fmaf(v[j], rstd, nb * u[j]);
+  } else if (e.row_stats) {                   // folded LayerNorm: per-row scale and rank-1 mean correction (include/cvb200.h)
     const float2 rs = __ldg(reinterpret_cast<const float2*>(e.row_stats) + m);
     float u[NV];
     vec_load_f32<NV>(e.row_u + n0, u);
@@ -240,6 +258,14 @@ __device__ __forceinline__ void epi_apply(const Epi& e, size_t m, int b, bool va
   if (e.gn_stats) {
 #pragma unroll
     for (int j = 0; j < NV; ++j) { gsum += v[j]; gsq = fmaf(v[j], v[j], gsq); }
+  }
+  if (RP && e.row_parts_out) {         // statistics of the values AS STORED (what the consumer's MMA will read)
+#pragma unroll
+    for (int j = 0; j < NV; ++j) {
+      const float r = e.out0_dt == DT_BF16 ? __bfloat162float(__float2bfloat16(v[j])) : v[j];
+      gsum += r;
+      gsq = fmaf(r, r, gsq);
+    }
   }
   vec_store_dt<NV>(e.out0, m * e.ldo0 + col, e.out0_dt, v);
   if (e.out1_mode != OUT1_NONE) {

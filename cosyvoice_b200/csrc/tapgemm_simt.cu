@@ -106,6 +106,7 @@ int launch_tapgemm_simt(const GemmParams& p, cudaStream_t stream) {
   CVB_REQUIRE(p.seg_len % BK == 0, "seg_len must be a multiple of 16");
   CVB_REQUIRE(p.n_phase * p.n_seg <= MAX_SEGS, "too many segments");
   CVB_REQUIRE(p.m_tiles > 0, "empty problem");
+  CVB_REQUIRE(!p.epi.row_parts && !p.epi.row_parts_out, "row_parts / row_parts_out: tcgen05 engine only");
   CVB_TRY(check_epilogue_layout(p));
   dim3 grid(p.m_tiles, ceil_div(p.n_pad, BN), p.n_phase);
   if (p.dt == DT_BF16) CVB_CUDA(launch_pdl(tapgemm_simt_kernel<__nv_bfloat16>, dim3(grid), dim3(NT), 0, stream, p));

@@ -31,7 +31,7 @@ constexpr int NUM_THREADS = 64 + 32 * EPI_WARPS;
 constexpr int TMEM_COLS = 512;
 
 // One accumulator row (this thread's TMEM lane) of a tile: NV columns at a time.
-template <int NV>
+template <int NV, bool RP>
 __device__ __forceinline__ void epilogue_chunks(const GemmParams& p, uint32_t taddr, int bn, int n_base, size_t m, int b,
                                                 bool valid, int phase, int lane, int half) {
   float gs = 0.f, gq = 0.f;
@@ -39,7 +39,12 @@ __device__ __forceinline__ void epilogue_chunks(const GemmParams& p, uint32_t ta
     float v[NV];
     if constexpr (NV == 32) ptx::tmem_ld32(taddr + c, v);
     else ptx::tmem_ld16(taddr + c, v);
-    epi_apply<NV, false>(p.epi, m, b, valid, phase, n_base + c, v, gs, gq);
+    epi_apply<NV, false, RP>(p.epi, m, b, valid, phase, n_base + c, v, gs, gq);
+    if (RP && p.epi.row_parts_out && ((c + NV) & 31) == 0) {
+      // this thread's row, one finished 32-column chunk: (sum, sum of squares) for the consumer's folded LayerNorm
+      reinterpret_cast<float2*>(p.epi.row_parts_out)[m * 8 + ((n_base + c) >> 5)] = make_float2(gs, gq);
+      gs = gq = 0.f;
+    }
     if (p.epi.gn_stats && ((c + NV) & 31) == 0) {
       // one 32-channel GroupNorm group finished: reduce over the warp's 32 rows, one atomic pair per warp
       const float s = warp_sum(gs), q = warp_sum(gq);
@@ -53,6 +58,7 @@ __device__ __forceinline__ void epilogue_chunks(const GemmParams& p, uint32_t ta
   }
 }
 
+template <bool RP>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 tapgemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW,
                   const __grid_constant__ GemmParams p, const int resident) {
@@ -201,8 +207,8 @@ tapgemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
       ptx::mbar_wait(&tfull[acc], acc_ph);
       ptx::tc_fence_after();
       const uint32_t taddr = tmem_base + ((uint32_t)(lane_grp * 32) << 16) + acc * 256;
-      if ((bn & 31) == 0) epilogue_chunks<32>(p, taddr, bn, nt * bn, (size_t)m, b, valid, phase, lane, half);
-      else epilogue_chunks<16>(p, taddr, bn, nt * bn, (size_t)m, b, valid, phase, lane, half);
+      if ((bn & 31) == 0) epilogue_chunks<32, RP>(p, taddr, bn, nt * bn, (size_t)m, b, valid, phase, lane, half);
+      else epilogue_chunks<16, RP>(p, taddr, bn, nt * bn, (size_t)m, b, valid, phase, lane, half);
       ptx::tc_fence_before();
       ptx::mbar_arrive(&tempty[acc]);
       acc ^= 1;
@@ -283,6 +289,12 @@ int launch_tapgemm_tc(const GemmParams& p_in, cudaStream_t stream) {
   CVB_REQUIRE(p.m_tiles > 0, "empty problem");
   CVB_REQUIRE(p.bn >= 16 && p.bn <= 256 && p.bn % 16 == 0 && p.n_pad % p.bn == 0, "bad N tile");
   CVB_REQUIRE(!p.epi.gn_stats || p.bn % 32 == 0, "GroupNorm statistics need bn % 32 == 0");
+  const bool rp = p.epi.row_parts != nullptr || p.epi.row_parts_out != nullptr;
+  CVB_REQUIRE(!p.epi.row_parts_out || (p.N == 256 && p.n_pad == 256 && p.n_phase == 1 && p.bn % 32 == 0 && !p.epi.gn_stats &&
+                                       (reinterpret_cast<uintptr_t>(p.epi.row_parts_out) & 7) == 0),
+              "row_parts_out: N == 256, one phase, no GroupNorm statistics, 8-byte aligned");
+  CVB_REQUIRE(!p.epi.row_parts || (!p.epi.row_stats && p.epi.row_u && (reinterpret_cast<uintptr_t>(p.epi.row_parts) & 15) == 0),
+              "row_parts: needs row_u, excludes row_stats, 16-byte aligned");
   CVB_TRY(check_epilogue_layout(p));
   const int sms = num_sms();
   // Latency mode (streaming chunks: a handful of 128-row tiles): narrower N tiles put the problem on more SMs.
@@ -302,7 +314,9 @@ int launch_tapgemm_tc(const GemmParams& p_in, cudaStream_t stream) {
   static std::once_flag attr_once;
   static cudaError_t attr_err = cudaSuccess;
   std::call_once(attr_once, [] {
-    attr_err = cudaFuncSetAttribute(tapgemm_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
+    attr_err = cudaFuncSetAttribute(tapgemm_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
+    if (attr_err == cudaSuccess)
+      attr_err = cudaFuncSetAttribute(tapgemm_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
   });
   CVB_CUDA(attr_err);
   CUtensorMap tmA, tmW;
@@ -321,7 +335,10 @@ int launch_tapgemm_tc(const GemmParams& p_in, cudaStream_t stream) {
   } else {
     grid = total < sms ? total : sms;
   }
-  CVB_CUDA(launch_pdl(tapgemm_tc_kernel, dim3(grid), dim3(NUM_THREADS), SMEM_BYTES, stream, tmA, tmW, p, resident ? 1 : 0));
+  if (rp)
+    CVB_CUDA(launch_pdl(tapgemm_tc_kernel<true>, dim3(grid), dim3(NUM_THREADS), SMEM_BYTES, stream, tmA, tmW, p, resident ? 1 : 0));
+  else
+    CVB_CUDA(launch_pdl(tapgemm_tc_kernel<false>, dim3(grid), dim3(NUM_THREADS), SMEM_BYTES, stream, tmA, tmW, p, resident ? 1 : 0));
   CVB_LAUNCH_CHECK();
   return CVB_OK;
 }

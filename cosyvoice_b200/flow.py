@@ -93,6 +93,10 @@ class _Weights:
                         out=linear_plan(sd[p + "attn1.to_out.0.weight"], sd[p + "attn1.to_out.0.bias"], dtype, device),
                         ln3=(f32(p + "norm3.weight"), f32(p + "norm3.bias")),
                         ff1=linear_plan(sd[p + "ff.net.0.proj.weight"], sd[p + "ff.net.0.proj.bias"], dtype, device),
+                        # norm3 folded into FFN-in: small layouts, statistics from the out-projection's epilogue (row partials)
+                        ff1_f=(folded_linear_plan(sd[p + "ff.net.0.proj.weight"], sd[p + "ff.net.0.proj.bias"],
+                                                  sd[p + "norm3.weight"], sd[p + "norm3.bias"], dtype, device)
+                               if dtype == torch.bfloat16 else None),
                         ff2=linear_plan(sd[p + "ff.net.2.weight"], sd[p + "ff.net.2.bias"], dtype, device),
                         ffw=self._ffn_weights(sd, p, dtype, device))
 
@@ -154,6 +158,7 @@ class _Program:
         # 1 MB of FFN weights per 128-row tile from L2 (~10 TB/s over 148 SMs) and the out-projection adds 384 KB per tile to
         # that stream, so it stays off by default.
         self.fused_out = os.environ.get("CVB200_FUSED_OUT", "0") == "1"
+        self.fold_parts = os.environ.get("CVB200_FOLD_PARTS", "1") == "1"
         R, S = lay.rows, lay.n_seq
         z = lambda *shape, dtype=dt: torch.zeros(*shape, dtype=dtype, device=dev)
         self.t = z(S, dtype=torch.float32)
@@ -173,6 +178,7 @@ class _Program:
         self.X = z(R, C, dtype=torch.float32 if os.environ.get("CVB200_RESIDUAL", "act") == "f32" else dt)
         self.n = z(R, C)
         self.row_stats = z(R, 2, dtype=torch.float32)       # (rstd, -mean rstd) of the stream's rows, left by block_ffn
+        self.row_parts = z(R, 8, 2, dtype=torch.float32)    # (sum, sum of squares) per 32-column chunk, left by a GEMM epilogue
         self.qkv, self.o, self.f = z(R, 3 * HEADS * HEAD_DIM), z(R, HEADS * HEAD_DIM), z(R, 4 * C)
         self.s_in = z(R, C)
         self.fin = z(R, C)
@@ -270,7 +276,16 @@ class _Program:
         self.ops.append(ops.norm_mish_op(h, hn, r["b1"]["gamma"], r["b1"]["beta"], L, gn_stats=s1, seq_bias=tb))
         self._gemm(r["b2"]["conv"], hn, L, h, gn_stats=s2)
         self.ops.append(ops.norm_mish_op(h, hn, r["b2"]["gamma"], r["b2"]["beta"], L, gn_stats=s2))
-        self._gemm(r["res"], A, L, X, res=hn)
+        # Small layouts on the bf16 tcgen05 engine (where block_ffn is not selected): both LayerNorms of every block are
+        # folded into the GEMM that follows, with the row statistics handed over as partial sums by the GEMM that WROTE the
+        # stream (epilogue.row_parts_out -> row_parts): 2 of a block's 7 launches go, which is what a streaming chunk is
+        # made of (launch latency, not FLOPs).  CVB200_FOLD_PARTS=0 restores the LayerNorm launches.
+        fuse = (self.fused_ffn and X.dtype == torch.bfloat16 and L.m_tiles >= self.fused_ffn_min_tiles
+                and all(t["ffw"] is not None for t in st["tbs"]))
+        parts_path = (not fuse and self.fold_parts and self.engine == _lib.ENGINE_TCGEN05 and X.dtype == torch.bfloat16
+                      and all(t["qkv_f"] is not None and t["ff1_f"] is not None for t in st["tbs"]))
+        parts = self.row_parts[:R] if parts_path else None
+        self._gemm(r["res"], A, L, X, res=hn, **(dict(row_parts_out=parts) if parts_path else {}))
         if r["index"] == 0:
             self.taps["down0.resnet"] = (self.X, L)
         qkv, o, f = self.qkv[:R], self.o[:R], self.f[:R]
@@ -280,8 +295,6 @@ class _Program:
         # column: below ~40 tiles the four launches win inside a CUDA graph (streaming chunk 30.6 vs 34.3 ms,
         # profiles/r02_ffn_rows_sweep.txt).  The choice depends on the STRIDE pattern only (L.m_tiles), so every call of
         # a program takes the same kernels and batch members stay independent of their neighbours.
-        fuse = (self.fused_ffn and X.dtype == torch.bfloat16 and L.m_tiles >= self.fused_ffn_min_tiles
-                and all(t["ffw"] is not None for t in st["tbs"]))
         stats = self.row_stats[:R]
         for k, t in enumerate(st["tbs"]):
             # components/transformer.py:262-316
@@ -290,6 +303,9 @@ class _Program:
                 # norm1 folded into the projection: the previous block's kernel left (rstd, -mean rstd) of every row
                 pf = t["qkv_f"]
                 self._gemm(pf, X, L, qkv, row_stats=stats, row_u=pf.extra["row_u"])
+            elif parts_path:
+                pf = t["qkv_f"]
+                self._gemm(pf, X, L, qkv, row_parts=parts, row_u=pf.extra["row_u"])
             else:
                 self.ops.append(ops.layernorm_op(X, n, t["ln1"][0], t["ln1"][1], R))
                 self._gemm(t["qkv"], n, L, qkv, bias=False)
@@ -309,6 +325,13 @@ class _Program:
                 self.ops.append(ops.block_ffn_op(X, w1f, u1, b1f, w2, b2, L, flops=fl, out1=last_copy if last else None,
                                                  stats_out=None if last else stats, **kw))
                 self.flops += fl
+                continue
+            if parts_path:
+                self._gemm(t["out"], o, L, X, res=X, row_parts_out=parts)
+                pf = t["ff1_f"]
+                self._gemm(pf, X, L, f, act=_lib.ACT_GELU, row_parts=parts, row_u=pf.extra["row_u"])
+                kw = dict(out1=last_copy, out1_mode=_lib.OUT1_COPY) if last else dict(row_parts_out=parts)
+                self._gemm(t["ff2"], f, L, X, res=X, **kw)
                 continue
             self._gemm(t["out"], o, L, X, res=X)
             self.ops.append(ops.layernorm_op(X, n, t["ln3"][0], t["ln3"][1], R))

@@ -111,7 +111,8 @@ def gemm_op(plan: TapPlan, A: torch.Tensor, lay: SeqLayout, out0: torch.Tensor, 
             out1: Optional[torch.Tensor] = None, out1_mode: int = _lib.OUT1_NONE,
             out1_alpha: Optional[torch.Tensor] = None, out1_slope: float = 0.0,
             gn_stats: Optional[torch.Tensor] = None, row_stats: Optional[torch.Tensor] = None,
-            row_u: Optional[torch.Tensor] = None, flops: int = 0) -> Op:
+            row_u: Optional[torch.Tensor] = None, row_parts: Optional[torch.Tensor] = None,
+            row_parts_out: Optional[torch.Tensor] = None, row_eps: float = 1e-5, flops: int = 0) -> Op:
     """A: 2-D time-major tensor (possibly a column slice view) whose rows follow the layout of the
     INPUT signal; `lay` is the M-space layout (output rows / n_phase).  out0/out1/res: 2-D tensors
     whose row r, column block [phase*phase_col, +N) receive M-row r of that phase."""
@@ -162,8 +163,17 @@ def gemm_op(plan: TapPlan, A: torch.Tensor, lay: SeqLayout, out0: torch.Tensor, 
         assert row_stats.dtype == torch.float32 and row_stats.is_contiguous() and row_stats.shape[-1] == 2
         assert row_u is not None and row_u.dtype == torch.float32 and row_u.numel() >= plan.n_pad
         e.row_stats, e.row_u = row_stats.data_ptr(), row_u.data_ptr()
+    if row_parts is not None:        # folded LayerNorm from the producing GEMM's partial sums [rows, 8, 2]
+        assert row_stats is None and row_u is not None and row_u.dtype == torch.float32 and row_u.numel() >= plan.n_pad
+        assert row_parts.dtype == torch.float32 and row_parts.is_contiguous() and row_parts.shape[-2:] == (8, 2)
+        e.row_parts, e.row_u, e.row_eps = row_parts.data_ptr(), row_u.data_ptr(), row_eps
+    if row_parts_out is not None:    # (sum, sum of squares) per 32-column chunk of the stored rows, for the consumer's fold
+        assert row_parts_out.dtype == torch.float32 and row_parts_out.is_contiguous() and row_parts_out.shape[-2:] == (8, 2)
+        assert plan.N == 256 and plan.n_phase == 1 and gn_stats is None
+        e.row_parts_out = row_parts_out.data_ptr()
     lib = _lib.load()
-    keep = (plan, A, lay, out0, seq_len, out_limit, seq_bias, act_alpha, res, out1, out1_alpha, gn_stats, row_stats, row_u)
+    keep = (plan, A, lay, out0, seq_len, out_limit, seq_bias, act_alpha, res, out1, out1_alpha, gn_stats, row_stats, row_u,
+            row_parts, row_parts_out)
 
     def run(_g=g, _keep=keep):
         _lib.check(lib.cvb200_tapgemm(C.byref(_g), engine, _stream()), "tapgemm")

@@ -91,6 +91,16 @@ typedef struct cvb200_epilogue {
    * before the bias, with row_stats[m] = (rstd, -mean * rstd) of input row m, row_u[n] = sum_k W[n][k], bias = b + W . beta */
   const float* row_stats;  /* [rows][2] or NULL */
   const float* row_u;      /* [n_pad] */
+  /* The same fold with the statistics carried as PARTIAL sums, so that the GEMM that PRODUCES a 256-wide row stream can hand
+   * them to the GEMM that consumes it and no LayerNorm launch is left (small layouts, where launches are the cost):
+   *   row_parts_out[m][n/32] = (sum, sum of squares) of the stored (rounded) values of columns [32 (n/32), +32) of output row m
+   *                            -- written by a GEMM with N == 256, n_phase == 1;
+   *   row_parts[m][0..8)     -- read by the consumer: mean = sum/256, rstd = rsqrt(sumsq/256 - mean^2 + row_eps), then as
+   *                            row_stats.  tcgen05 engine only. */
+  const float* row_parts;  /* [rows][8][2] or NULL (excludes row_stats) */
+  float* row_parts_out;    /* [rows][8][2] or NULL */
+  float row_eps;
+  int32_t reserved0;
 } cvb200_epilogue;
 
 /* The one contraction of the library ("tap GEMM"):

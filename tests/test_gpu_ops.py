@@ -602,3 +602,54 @@ def test_folded_layernorm_projection_matches_layernorm_then_projection():
         err = (out[r0:r0 + l].float() - want[r0:r0 + l]).abs().max().item()
         assert err < 3e-2 * max(1.0, want[r0:r0 + l].abs().max().item()), (b, err)
         assert out[r0 + l:r0 + lay.strides[b]].float().abs().max().item() == 0
+
+
+@pytest.mark.parametrize("lens", [[300, 77, 640], [50], [609] * 12])
+def test_row_partials_fold_layernorm_between_two_gemms(lens):
+    """epilogue.row_parts_out / row_parts: a 256-wide GEMM (out-projection + bf16 residual) hands (sum, sum of squares) per
+    32-column chunk of the rows IT STORES to the next GEMM, which folds LayerNorm from them -- no LayerNorm launch in between.
+    Checked: the partial sums against torch on the stored stream; the consumer against the row_stats path fed with torch's
+    statistics of the same stream (identical operands, so only the variance formula differs) and against torch's
+    LayerNorm -> Linear.  The small case runs in the GEMM's latency mode (64-wide N tiles: two chunks per tile)."""
+    from cosyvoice_b200.packing import folded_linear_plan
+    torch.manual_seed(47)
+    lay = SeqLayout.build(lens, DEV)
+    R = lay.rows
+    x0 = torch.zeros(R, 256, device=DEV)
+    o = torch.zeros(R, 512, device=DEV)
+    for b, l in enumerate(lens):
+        x0[lay.row0[b]:lay.row0[b] + l] = torch.randn(l, 256, device=DEV) * 1.3 + 2 * torch.randn(l, 1, device=DEV)
+        o[lay.row0[b]:lay.row0[b] + l] = torch.randn(l, 512, device=DEV)
+    x0, o = x0.to(torch.bfloat16), o.to(torch.bfloat16)
+    p_out = linear_plan(torch.randn(256, 512) * (1.0 / 512) ** 0.5, torch.randn(256) * 0.1, torch.bfloat16, DEV)
+    w = torch.randn(1536, 256) * 0.06
+    g, be = 1 + 0.2 * torch.randn(256), 0.1 * torch.randn(256)
+    pf = folded_linear_plan(w, None, g, be, torch.bfloat16, DEV)
+    x = x0.clone()
+    parts = torch.full((R, 8, 2), 7.0, device=DEV)
+    ops.gemm_op(p_out, o, lay, x, engine=_lib.ENGINE_TCGEN05, res=x, row_parts_out=parts)()
+    # the producer's other outputs are unchanged by the extra side output
+    x_ref = x0.clone()
+    ops.gemm_op(p_out, o, lay, x_ref, engine=_lib.ENGINE_TCGEN05, res=x_ref)()
+    _sync()
+    assert torch.equal(x, x_ref)
+    xf = x.float().reshape(R, 8, 32)
+    assert torch.allclose(parts[..., 0], xf.sum(-1), rtol=1e-5, atol=1e-3)
+    assert torch.allclose(parts[..., 1], (xf * xf).sum(-1), rtol=1e-5, atol=1e-3)
+    # consumer: partial sums vs finished statistics
+    q1 = torch.zeros(R, 1536, device=DEV, dtype=torch.bfloat16)
+    ops.gemm_op(pf, x, lay, q1, engine=_lib.ENGINE_TCGEN05, row_parts=parts, row_u=pf.extra["row_u"])()
+    xr = x.float()
+    mean, rstd = xr.mean(dim=1), torch.rsqrt(xr.var(dim=1, unbiased=False) + 1e-5)
+    q2 = torch.zeros(R, 1536, device=DEV, dtype=torch.bfloat16)
+    ops.gemm_op(pf, x, lay, q2, engine=_lib.ENGINE_TCGEN05, row_stats=torch.stack([rstd, -mean * rstd], 1).contiguous(),
+                row_u=pf.extra["row_u"])()
+    _sync()
+    want = torch.nn.functional.layer_norm(xr, (256,), g.to(DEV), be.to(DEV)) @ w.to(DEV).t()
+    for b, l in enumerate(lens):
+        r0 = lay.row0[b]
+        scale = max(1.0, want[r0:r0 + l].abs().max().item())
+        assert (q1[r0:r0 + l].float() - q2[r0:r0 + l].float()).abs().max().item() < 2e-2 * scale, b      # a bf16 ulp or two
+        assert (q1[r0:r0 + l].float() - want[r0:r0 + l]).abs().max().item() < 3e-2 * scale, b
+        assert q1[r0 + l:r0 + lay.strides[b]].float().abs().max().item() == 0
+        assert parts[r0 + l:r0 + lay.strides[b]].abs().max().item() == 0

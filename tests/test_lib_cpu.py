@@ -47,7 +47,7 @@ def test_ops_refuse_cpu_tensors(lib):
 def test_struct_sizes_match_c_layout():
     import ctypes as C
     # 8 pointers + 16 4-byte fields + 2 pointers (folded-LayerNorm row statistics)
-    assert C.sizeof(_lib.Epilogue) == 8 * 8 + 16 * 4 + 2 * 8
+    assert C.sizeof(_lib.Epilogue) == 8 * 8 + 16 * 4 + 2 * 8 + 2 * 8 + 2 * 4
     assert C.sizeof(_lib.Layout) == 4 * 8 + 3 * 4 + 4
     assert C.sizeof(_lib.Gemm) == 6 * 8 + 11 * 4 + 2 * 2 * 32 + 4 + C.sizeof(_lib.Epilogue)
 
