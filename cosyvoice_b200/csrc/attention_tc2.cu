@@ -184,14 +184,10 @@ attention_tc2_kernel(const __grid_constant__ CUtensorMap tm, const __grid_consta
     ptx::prefetch_tensormap(&tmkv);
   }
   if (warp == MMA_WARP) ptx::tmem_alloc(tmem_slot, TM_COLS);
-  ptx::tc_fence_before();
-  __syncthreads();
-  ptx::tc_fence_after();
-  const uint32_t tmem = *tmem_slot;
-  pdl_trigger();      // programmatic dependent launch: the prologue above overlapped the previous kernel's tail
-  pdl_wait();
-
   // Items are dealt round-robin to the 2 * gridDim.x slots of the grid: slot s of CTA c takes items 2c + s, + 2 gridDim.x, ...
+  // The table is built BEFORE the programmatic-dependency wait: the layout arrays are not written by the preceding kernel
+  // (lengths are re-bound by a copy that the stream orders before it), so the two dependent L2 round trips per item
+  // overlap the previous kernel's tail -- what a streaming chunk's 560 small attention launches are mostly made of.
   const int it_step = SLOTS * (int)gridDim.x;
   const int per_slot = (n_items - SLOTS * (int)blockIdx.x + it_step - 1) / it_step;     // items of slot 0 (slot 1: <= this)
   for (int idx = threadIdx.x; idx < SLOTS * per_slot; idx += NUM_THREADS) {
@@ -202,7 +198,13 @@ attention_tc2_kernel(const __grid_constant__ CUtensorMap tm, const __grid_consta
     if (it < n_items) w = attn_item(lay, it, heads);
     table[s * MAX_ITEMS + k] = w;
   }
+  ptx::tc_fence_before();
   __syncthreads();
+  ptx::tc_fence_after();
+  const uint32_t tmem = *tmem_slot;
+  pdl_trigger();      // programmatic dependent launch: the prologue above overlapped the previous kernel's tail
+  pdl_wait();
+
   auto seek = [&](Cursor& c, int s) {
     for (; c.k < per_slot; ++c.k) {
       c.w = table[s * MAX_ITEMS + c.k];
