@@ -49,7 +49,10 @@ constexpr int KV_STAGES = 2;
 constexpr int Q_BUFS = 2;                                            // the next item's Q tile is fetched during the current item
 constexpr int SLOT_SMEM = Q_BYTES * Q_BUFS + 2 * KV_BYTES * KV_STAGES;     // Q x 2 + K ring + V ring
 constexpr int SLOT_BARS = 20;                                        // mbarriers per slot
-constexpr int MAX_ITEMS = 256;                                       // per slot: the CTA's item table lives in shared memory
+#ifndef ATTN2_MAX_ITEMS
+#define ATTN2_MAX_ITEMS 256
+#endif
+constexpr int MAX_ITEMS = ATTN2_MAX_ITEMS;                           // per slot: the CTA's item table lives in shared memory
 constexpr int SMEM_BYTES = 1024 + SLOTS * SLOT_SMEM + SLOTS * SLOT_BARS * 8 + 64 + SLOTS * MAX_ITEMS * 16;
 static_assert(SMEM_BYTES <= 227 * 1024, "shared memory");
 // TMEM columns of a slot: S [0, BK) fp32, P [BK, BK + BK/2) packed bf16, O [.., +64) fp32
@@ -156,7 +159,7 @@ struct Cursor {
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 attention_tc2_kernel(const __grid_constant__ CUtensorMap tm, const __grid_constant__ CUtensorMap tmkv,
                      __nv_bfloat16* __restrict__ out, int ldo, const Layout lay,
-                     int heads, float scale_log2, int n_items) {
+                     int heads, float scale_log2, int item0, int n_items) {
   const int inner = heads * HD;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -195,7 +198,7 @@ attention_tc2_kernel(const __grid_constant__ CUtensorMap tm, const __grid_consta
     const int it = SLOTS * (int)blockIdx.x + s + k * it_step;
     AttnItem w;
     w.head = 0; w.q0 = 0; w.len = 0; w.seq0 = 0;
-    if (it < n_items) w = attn_item(lay, it, heads);
+    if (it < n_items) w = attn_item(lay, item0 + it, heads);
     table[s * MAX_ITEMS + k] = w;
   }
   ptx::tc_fence_before();
@@ -554,10 +557,14 @@ int launch_attention_tc2(const void* qkv, int ld, void* out, int ldo, const Layo
   const int sms = device_sm_count();
   const int want = (n_items + SLOTS - 1) / SLOTS;
   const int grid = want < sms ? want : sms;
-  CVB_REQUIRE((n_items + SLOTS * grid - 1) / (SLOTS * grid) <= MAX_ITEMS, "too many query tiles for the per-CTA item table");
-  CVB_CUDA(launch_pdl(attention_tc2_kernel, dim3(grid), dim3(NUM_THREADS), SMEM_BYTES, st, tm, tmkv,
-                      reinterpret_cast<__nv_bfloat16*>(out), ldo, lay, heads, scale * 1.4426950408889634f, n_items));
-  CVB_LAUNCH_CHECK();
+  // a CTA's item table holds MAX_ITEMS entries per work stream: larger problems go out as several launches
+  const int per_launch = MAX_ITEMS * SLOTS * grid;
+  for (int item0 = 0; item0 < n_items; item0 += per_launch) {
+    const int n = n_items - item0 < per_launch ? n_items - item0 : per_launch;
+    CVB_CUDA(launch_pdl(attention_tc2_kernel, dim3(grid), dim3(NUM_THREADS), SMEM_BYTES, st, tm, tmkv,
+                        reinterpret_cast<__nv_bfloat16*>(out), ldo, lay, heads, scale * 1.4426950408889634f, item0, n));
+    CVB_LAUNCH_CHECK();
+  }
   return CVB_OK;
 }
 
