@@ -120,7 +120,10 @@ __device__ __forceinline__ float mish_fast(float x) {
 // ROWS rows per warp (all inside one 128-row tile = one sequence): the GroupNorm statistics are turned into (mean, rstd)
 // in fp64 ONCE per warp instead of once per row -- fp64 division and square root run at 1/64 rate on this part, and were
 // most of the 30 us this kernel took at 40 960 rows (round-1 launch list) for 42 MB of traffic.
-template <int ROWS>
+// FASTGN: the bf16 engine's GroupNorm case as its own instantiation (bf16 output, fast Mish): the affine part collapses to
+// one FFMA per element (a = rstd * gamma, c = beta - mean * a, per lane, once) and no runtime branch sits in the element
+// loop; the generic instantiation carried both Mish variants and both normalisations behind branches in every element.
+template <int ROWS, bool FASTGN>
 __global__ void __launch_bounds__(256) norm_mish256_kernel(const void* __restrict__ h, int ldh, int h_dt,
                                                            void* __restrict__ out, int ldo, int out_dt,
                                                            const float* __restrict__ gamma, const float* __restrict__ beta,
@@ -132,38 +135,74 @@ __global__ void __launch_bounds__(256) norm_mish256_kernel(const void* __restric
   const int lane = threadIdx.x & 31;
   if (row0 >= lay.rows) return;
   const int tile = row0 >> 7;
+  // the rows are requested before the tile -> sequence -> length lookup (two dependent L2 round trips) has come back: pad
+  // rows lie inside the buffer and are discarded below
+  float v[ROWS][8];
+#pragma unroll
+  for (int r = 0; r < ROWS; ++r) load8_dt(h, (size_t)(row0 + r) * ldh + lane * 8, h_dt, v[r]);
   const int b = __ldg(lay.tile_seq + tile);
   const int lrow0 = __ldg(lay.tile_row0 + tile) + (row0 & 127);
   const int len = __ldg(lay.seq_len + b);
-  float v[ROWS][8];
-#pragma unroll
-  for (int r = 0; r < ROWS; ++r) {
-    if (lrow0 + r < len) load8_dt(h, (size_t)(row0 + r) * ldh + lane * 8, h_dt, v[r]);
-    else {
-#pragma unroll
-      for (int i = 0; i < 8; ++i) v[r][i] = 0.f;
-    }
-  }
   float gmean = 0.f, grstd = 0.f;
+  __shared__ float2 s_stat[8];
   if (gn_stats) {
-    // GroupNorm(8, 256): group = 32 channels = 4 lanes; statistics over 32 channels x len frames
-    const int g = lane >> 2;
-    const double n = (double)len * 32.0;
-    const double s = gn_stats[((size_t)b * 8 + g) * 2], q = gn_stats[((size_t)b * 8 + g) * 2 + 1];
-    const double m = s / n;
-    double var = q / n - m * m;
-    if (var < 0.0) var = 0.0;
-    gmean = (float)m;
-    grstd = (float)(1.0 / sqrt(var + (double)eps));
+    // GroupNorm(8, 256): group = 32 channels = 4 lanes; statistics over 32 channels x len frames.  The block's rows lie in
+    // one 128-row tile = one sequence, so the eight (mean, rstd) pairs are computed by eight threads and shared.
+    if (threadIdx.x < 8) {
+      // fp64 WITHOUT fp64 division or square root (each expands to ~30 dependent fp64 instructions and the fp64 pipe of
+      // this part is narrow: two divisions and a sqrt per warp were a fifth of the kernel's 20 us at 40 960 rows): fp32
+      // reciprocal / rsqrt seeds refined by one Newton step in fp64 (relative error ~1e-14).
+      const int g = threadIdx.x;
+      const double n = (double)len * 32.0;
+      const double s = gn_stats[((size_t)b * 8 + g) * 2], q = gn_stats[((size_t)b * 8 + g) * 2 + 1];
+      double rn = (double)(1.f / (float)n);
+      rn = rn * (2.0 - n * rn);
+      const double m = s * rn;
+      double var = q * rn - m * m;
+      if (var < 0.0) var = 0.0;
+      const double ve = var + (double)eps;
+      double y = (double)rsqrtf((float)ve);
+      y = y * (1.5 - 0.5 * ve * y * y);
+      s_stat[g] = make_float2((float)m, (float)y);
+    }
+    __syncthreads();
+    gmean = s_stat[lane >> 2].x;
+    grstd = s_stat[lane >> 2].y;
   }
   float g8[8], b8[8], t8[8];
   load8<float>(gamma + lane * 8, g8);
   load8<float>(beta + lane * 8, b8);
   if (seq_bias) load8<float>(seq_bias + (size_t)b * seq_bias_ld + lane * 8, t8);
   const bool fast = out_dt == DT_BF16;
+  if constexpr (FASTGN) {
+    float a8[8], c8[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      a8[i] = grstd * g8[i];
+      c8[i] = fmaf(-gmean, a8[i], b8[i]);
+    }
+#pragma unroll
+    for (int r = 0; r < ROWS; ++r) {
+      const bool ok = lrow0 + r < len;
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        // Mish without the large-x select: for y > 20 the ratio below is exactly 1 in fp32
+        const float y = fmaf(v[r][i], a8[i], c8[i]);
+        const float u = __expf(fminf(y, 20.f));
+        const float n = u * (u + 2.f);
+        float o = y * __fdividef(n, n + 2.f);
+        if (seq_bias) o += t8[i];
+        v[r][i] = ok ? o : 0.f;
+      }
+      store8(out, (size_t)(row0 + r) * ldo + lane * 8, out_dt, v[r]);
+    }
+    return;
+  }
 #pragma unroll
   for (int r = 0; r < ROWS; ++r) {
-    if (lrow0 + r >= len) {                  // v[r] is zero: pad rows are written as zeros
+    if (lrow0 + r >= len) {                  // pad rows are written as zeros
+#pragma unroll
+      for (int i = 0; i < 8; ++i) v[r][i] = 0.f;
       store8(out, (size_t)(row0 + r) * ldo + lane * 8, out_dt, v[r]);
       continue;
     }
@@ -437,12 +476,18 @@ int launch_norm_mish(const void* h, int ldh, int h_dt, void* out, int ldo, int o
   CVB_REQUIRE(C == 256, "Norm+Mish kernel is specialised for 256 channels");
   CVB_REQUIRE(ldh % 8 == 0 && ldo % 8 == 0, "leading dimensions must keep 16-byte alignment");
   if (lay.rows <= 0) return CVB_OK;
-  if (lay.rows >= 16384)
-    CVB_CUDA(launch_pdl(norm_mish256_kernel<4>, dim3(ceil_div(lay.rows, 32)), dim3(256), 0, st, h, ldh, h_dt, out, ldo, out_dt, gamma,
-                        beta, gn_stats, seq_bias, seq_bias_ld, lay, eps));
-  else
-    CVB_CUDA(launch_pdl(norm_mish256_kernel<1>, dim3(ceil_div(lay.rows, 8)), dim3(256), 0, st, h, ldh, h_dt, out, ldo, out_dt, gamma,
-                        beta, gn_stats, seq_bias, seq_bias_ld, lay, eps));
+  const bool fastgn = gn_stats != nullptr && out_dt == DT_BF16;
+#define CVB_NM(R_, F_)                                                                                                         \
+  CVB_CUDA(launch_pdl(norm_mish256_kernel<R_, F_>, dim3(ceil_div(lay.rows, 8 * R_)), dim3(256), 0, st, h, ldh, h_dt, out, ldo, \
+                      out_dt, gamma, beta, gn_stats, seq_bias, seq_bias_ld, lay, eps))
+  if (lay.rows >= 16384) {
+    if (fastgn) CVB_NM(4, true);
+    else CVB_NM(4, false);
+  } else {
+    if (fastgn) CVB_NM(1, true);
+    else CVB_NM(1, false);
+  }
+#undef CVB_NM
   CVB_LAUNCH_CHECK();
   return CVB_OK;
 }
