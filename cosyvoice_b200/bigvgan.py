@@ -184,8 +184,7 @@ class B200BigVGAN:
     def program(self, lens) -> _Program:
         key = tuple(int(l) for l in lens)
         if key not in self._programs:
-            if len(self._programs) >= 4:
-                self._programs.pop(next(iter(self._programs)))      # holders of the evicted program keep it alive
+            ops.trim_cache(self._programs, self.device, 4)          # LRU by count and memory; holders keep evicted programs alive
             self._programs[key] = _Program(self, key)
         return self._programs[key]
 

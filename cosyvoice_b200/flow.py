@@ -15,6 +15,7 @@ and a whole solve is a flat list of kernel launches that can be replayed from a 
 """
 import math
 import os
+import weakref
 from typing import Dict, List, Optional, Sequence, Tuple
 
 import torch
@@ -380,6 +381,7 @@ class B200Estimator:
         self.weights = _Weights(state_dict, causal, dtype, self.device)
         self.static_chunk_size = 0          # attribute written by cli/model.py:50,315
         self._programs: Dict[tuple, _Program] = {}
+        self._cfms = weakref.WeakSet()       # solvers on this estimator: their CUDA graphs pin programs (see program())
         self.serial = ops.Serial()          # programs and solver state are shared scratch: one user at a time
 
     def layout_for(self, lens: Sequence[int]) -> SeqLayout:
@@ -392,11 +394,12 @@ class B200Estimator:
         key = lay.stride_key()
         p = self._programs.pop(key, None)
         if p is None:
-            if len(self._programs) >= 32:
-                # LRU: the dict is kept in use order (hits are re-inserted below).  The evicted program is only dropped
-                # from the cache, not torn down: holders of a reference (AcousticBackend.prepare_resident*, a captured
-                # CUDA graph) keep a consistent object and its HBM is returned when the last reference goes.
-                self._programs.pop(next(iter(self._programs)))
+            # LRU, bounded by count and by memory (ops.trim_cache).  An evicted program is only dropped from the cache, not torn
+            # down: holders of a reference (AcousticBackend.prepare_resident*, a captured CUDA graph) keep a consistent object
+            # and its HBM is returned when the last reference goes.  Graphs pin their programs, so they are trimmed first.
+            for cfm in list(self._cfms):
+                ops.trim_cache(cfm._graphs, self.device, 33)
+            ops.trim_cache(self._programs, self.device, 32)
             p = _Program(self.weights, SeqLayout(lay.lens, lay.strides, self.device), self.engine)
         else:
             p.set_lens(lay.lens)
@@ -468,6 +471,7 @@ class B200ConditionalCFM:
     def __init__(self, estimator: B200Estimator, inference_cfg_rate: float = 0.7, t_scheduler: str = "cosine",
                  sigma_min: float = 1e-6):
         self.estimator = estimator
+        estimator._cfms.add(self)
         self.inference_cfg_rate = inference_cfg_rate
         self.t_scheduler = t_scheduler
         self.sigma_min = sigma_min
@@ -553,8 +557,7 @@ class B200ConditionalCFM:
                 self._steps(prog, st, ts, dts, table)
             n_launch = _lib.launch_count() - n0
             st["x"].copy_(keep)
-            if len(self._graphs) >= 32:
-                self._graphs.pop(next(iter(self._graphs)))          # least recently used
+            ops.trim_cache(self._graphs, self.estimator.device, 32)     # least recently used first; count and memory
             g = (graph, prog, n_launch, table)       # the graph reads `table`: keep it alive with the graph
         self._graphs[key] = g                                        # (re-)insert at the most-recent end
         self.last_graph_launches = g[2]

@@ -335,8 +335,7 @@ class _FlowBase:
         key = (tok.stride_key(), mel.stride_key(), chunk)
         p = self._programs.pop(key, None)
         if p is None:
-            if len(self._programs) >= 32:
-                self._programs.pop(next(iter(self._programs)))      # LRU; holders of the evicted program keep it alive
+            ops.trim_cache(self._programs, self.device, 32)         # LRU by count and memory; holders keep evicted programs alive
             p = _Program(self.weights, tok, mel, self.engine, chunk)
         self._programs[key] = p
         return p

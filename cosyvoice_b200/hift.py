@@ -309,8 +309,7 @@ class B200HiFTGenerator:
             key = (max(key),) * len(key)
         p = self._programs.pop(key, None)
         if p is None:
-            if len(self._programs) >= 8:
-                self._programs.pop(next(iter(self._programs)))      # LRU; holders of the evicted program keep it alive
+            ops.trim_cache(self._programs, self.device, 8)          # LRU by count and memory; holders keep evicted programs alive
             p = _Program(self.weights, lens, self.engine, strides=key, sampling_rate=float(self.sampling_rate),
                          audio_limit=float(self.audio_limit))
         else:

@@ -58,6 +58,22 @@ class Serial:
             self._lock.release()
         return False
 
+# Program / graph caches are LRU dicts bounded by a count AND by memory: a program for a 48 K-row batch holds ~1.5 GB of
+# pre-sized buffers, and a ragged sweep walks through dozens of stride buckets (at a 96 K-row budget the count-only caches
+# filled 178 GB).  Before a cache grows, its least-recently-used entries go while the process holds more than
+# CACHE_MEMORY_FRACTION of the device's memory; holders of an evicted program keep it alive and consistent.
+CACHE_MEMORY_FRACTION = 0.5
+
+
+def trim_cache(cache: dict, device, max_entries: int, keep: int = 1) -> None:
+    dev = torch.device(device)
+    limit = CACHE_MEMORY_FRACTION * torch.cuda.get_device_properties(dev).total_memory if dev.type == "cuda" else float("inf")
+    while len(cache) >= max_entries or (len(cache) > keep and dev.type == "cuda" and torch.cuda.memory_allocated(dev) > limit):
+        if not cache:
+            break
+        cache.pop(next(iter(cache)))
+
+
 # bench.py's roofline leg: when a list is installed here, every GEMM / attention launch is bracketed by CUDA
 # events on the launching stream and (kind, algorithmic_flops, start, end) is appended to it.
 PROFILE = None

@@ -193,3 +193,30 @@ def test_evicted_estimator_programs_are_reclaimed_by_reference_counting():
         assert all(r() is not None for r in refs[2:])
     finally:
         gc.enable()
+
+
+def test_caches_trimmed_by_memory_give_the_same_results(monkeypatch):
+    """ops.trim_cache: with the memory bound forced to zero every new stride bucket evicts all older programs and graphs
+    (the situation of a ragged sweep on a nearly full GPU); results are bit-identical to the unbounded run and the caches
+    stay at two entries."""
+    from cosyvoice_b200 import ops as ops_mod
+    sd = init_weights.flow_estimator_sd(False, seed=0)
+    g = torch.Generator().manual_seed(33)
+    cases = []
+    for l in (60, 330, 700, 60):          # stride buckets of 256, 512, 768 rows (v1 aligns to 256), then the first again
+        cases.append((torch.randn(1, 80, l, generator=g), torch.randn(1, 80, l, generator=g), torch.randn(1, 80, generator=g),
+                      torch.zeros(1, 80, l)))
+
+    def run():
+        est = B200Estimator(sd, causal=False, dtype=torch.bfloat16, device=DEV)
+        cfm = B200ConditionalCFM(est)
+        cfm.use_cuda_graph = True
+        outs = [cfm.solve_batch([mu], [spk], [cond], [z], 3)[0].clone() for mu, z, spk, cond in cases]
+        return outs, est, cfm
+    want, est0, _ = run()
+    assert len(est0._programs) == 3
+    monkeypatch.setattr(ops_mod, "CACHE_MEMORY_FRACTION", 0.0)
+    got, est1, cfm1 = run()
+    assert len(est1._programs) <= 2 and len(cfm1._graphs) <= 2      # the newest entry plus the one kept while it was built
+    for a, b in zip(got, want):
+        assert torch.equal(a, b)
