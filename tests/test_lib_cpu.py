@@ -69,3 +69,28 @@ def test_product_package_never_reaches_the_oracle():
             "try:\n    _lib.load()\nexcept RuntimeError as e:\n    print('LOUD', e)\n" % ROOT)
     out = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=120)
     assert "LOUD" in out.stdout and "not found" in out.stdout, out.stdout + out.stderr
+
+
+def test_cache_trim_and_async_staging_on_cpu():
+    """Host-side helpers that have a CPU meaning: ops.trim_cache bounds an LRU dict by count (oldest first, never below the
+    newest `keep` entries; the memory bound only exists on CUDA), and layout.to_device_async / copy_async_ are plain copies
+    when no CUDA device is involved."""
+    import torch
+    from cosyvoice_b200 import ops
+    from cosyvoice_b200.layout import SeqLayout, copy_async_, to_device_async
+    cache = {k: object() for k in range(5)}
+    ops.trim_cache(cache, "cpu", max_entries=4)
+    assert list(cache) == [2, 3, 4]                      # room for one more below the bound of 4
+    ops.trim_cache(cache, "cpu", max_entries=32)
+    assert list(cache) == [2, 3, 4]
+    ops.trim_cache(cache, "cpu", max_entries=1)
+    assert cache == {}
+    src = torch.arange(6, dtype=torch.int64)
+    out = to_device_async(src, "cpu", torch.int32)
+    assert out.dtype == torch.int32 and out.tolist() == list(range(6))
+    dst = torch.zeros(6, dtype=torch.float32)
+    copy_async_(dst, src)
+    assert dst.tolist() == [0.0, 1.0, 2.0, 3.0, 4.0, 5.0]
+    lay = SeqLayout.build([5, 130], "cpu")
+    lay.set_lens([7, 100])
+    assert lay.seq_len.tolist() == [7, 100] and lay.max_len == 100
