@@ -62,7 +62,7 @@ class Serial:
 # pre-sized buffers, and a ragged sweep walks through dozens of stride buckets (at a 96 K-row budget the count-only caches
 # filled 178 GB).  Before a cache grows, its least-recently-used entries go while the process holds more than
 # CACHE_MEMORY_FRACTION of the device's memory; holders of an evicted program keep it alive and consistent.
-CACHE_MEMORY_FRACTION = 0.5
+CACHE_MEMORY_FRACTION = 0.75
 
 
 def trim_cache(cache: dict, device, max_entries: int, keep: int = 1) -> None:
