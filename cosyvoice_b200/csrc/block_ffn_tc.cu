@@ -14,22 +14,32 @@
 // mean u exactly (same rounded weights), so the subtraction cancels it to fp32 accumulation error; x itself is not
 // re-rounded, which the unfused path does when it writes LN(x) as bf16.
 //
-// Warp roles (704 threads, one CTA per SM, persistent over 128-row tiles):
+// Warp roles (576 threads = 2 + BF_GELU_WARPS_N + BF_ROW_WARPS_N warps, one CTA per SM, persistent over 128-row tiles):
 //   warp 0       TMA producer: X tile -> smem (4 k-blocks of [128 x 64], 128B swizzle), W1' / W2 boxes -> 4 x 32 KB ring
-//   warp 1       single-thread tcgen05.mma issuer; per hidden chunk c of 128 units:
+//   warp 1       tcgen05.mma issuer (whole warp, one elected lane: ptx.cuh "lean issue path"); per hidden chunk c of 128 units:
 //                  G1(c): H[c%2] (TMEM fp32 128x128) = X(smem) . W1'[128c:128c+128, :]^T     16 x UMMA 128x128x16 (SS)
 //                  G2(c): O (TMEM fp32 128x256)     += Hbf16(TMEM) . W2[:, 128c:128c+128]^T   8 x UMMA 128x256x16 (TS)
 //                G1(c+1) is issued before G2(c)
-//   warps 2-17   GELU warps (thread = row x 32 hidden units): H -> rstd H - rstd mean u + b1' -> GELU -> bf16 written back in
-//                place into TMEM.  They do nothing else, so the chunk pipeline never waits for tile-boundary work; sixteen
-//                warps because the GELU chain is latency bound (eight warps measured 3.4k cycles per chunk).
-//   warps 18-21  row warps (thread = one whole row = its TMEM lane, no cross-thread exchange): row statistics of tile n+1
-//                from the smem tile while G2(7) of tile n / G1(0) of tile n+1 run; then the drain of tile n:
+//   GELU warps   (8 by default: thread = row x 64 hidden units, in 32-column slices): H -> rstd H - rstd mean u + b1' -> GELU ->
+//                bf16 written back in place into TMEM.  They do nothing else, so the chunk pipeline never waits for
+//                tile-boundary work.
+//   row warps    (8 by default: thread = half a row, halves merged through smem): row statistics of tile n+1 from the smem
+//                tile while G2(7) of tile n / G1(0) of tile n+1 run; then the drain of tile n:
 //                O + b2 + X (bf16, re-read from L2) -> bf16 X (+ copy) and the new row's statistics.
 // The elementwise work is what bounds this kernel (131 072 GELUs per tile against 16 384 cycles of MMA): it is written
 // in packed fp32x2 arithmetic (FFMA2 / FMUL2 / FADD2), 7 issue slots per hidden unit.
 //
-// TMEM: H0 [0,128) H1 [128,256) O [256,512).  smem: X tile 64 KB + 4 x 32 KB weight ring + vectors = 206 KB.
+// With OUTP (cvb200_block_out_ffn) the block's attention out-projection runs first, in the same kernel:
+//     X' = bf16((o . W_out^T + b_out) + X)            attn1.to_out[0] + residual, components/transformer.py:266-276
+// o [rows, 512] and W_out [256, 512] stream through the weight ring in 8 K steps of 64 (W_out slab, then o slab) into an
+// accumulator D0 that borrows the H0 | H1 columns (free until G1(0); the issuer first waits for the previous tile's last G2,
+// which still reads H).  The row warps turn D0 into the tile: X' replaces X_old in shared memory (generic-proxy writes +
+// fence.proxy.async before the MMA reads them), goes to global X (this thread reads it back as the drain's residual), and its
+// LayerNorm statistics are computed on the way; st_full then releases G1(0) and the GELU warps.  Arithmetic and order are those
+// of the separate out-projection GEMM's epilogue: the two forms are bit-identical (tests/test_gpu_ops.py).  Measured no faster
+// than the two launches, hence opt-in.
+//
+// TMEM: H0 [0,128) H1 [128,256) O [256,512).  smem: X tile 64 KB + 4 x 32 KB weight ring + vectors = 207 KB.
 #include <cuda.h>
 #include <cuda_bf16.h>
 
@@ -131,7 +141,7 @@ __device__ __forceinline__ void lds128f(uint32_t addr, float (&r)[4]) {
   asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(r[0]), "=f"(r[1]), "=f"(r[2]), "=f"(r[3]) : "r"(addr));
 }
 
-// OUTP: the block's attention out-projection runs first, inside this kernel (see the header comment, "with OUTP").
+// OUTP: the block's attention out-projection runs first, inside this kernel (header comment, "With OUTP").
 template <bool OUTP>
 __global__ void __launch_bounds__(BF_THREADS, 1)
 block_ffn_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CUtensorMap tmW1,
