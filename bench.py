@@ -326,7 +326,8 @@ def run_ours(args):
             h_out[b].copy_(w[0], non_blocking=True)
         torch.cuda.current_stream().synchronize()
     e2e_step()
-    ms_e2e = timed(e2e_step, max(1, K // 2))
+    e2e_step()                      # a second untimed pass: pinned staging blocks and program caches are warm
+    ms_e2e = timed(e2e_step, max(1, K))
     h2d = sum(a.numel() * 4 for seq in (h_toks, h_ptoks, h_pfeats, h_embs, h_zs) for a in seq)
     d2h = h_out.numel() * 4
 
