@@ -406,8 +406,12 @@ def run_ours(args):
                      "launches_per_step": tc["launches"], "kernel_ms_per_step": tc["ms"],
                      "share_of_eager_step": tc["ms"] / prof["_step_ms_eager"],
                      "kernels": {k: {"launches": d["launches"], "ms": round(d["ms"], 3),
-                                     "tflops": round(d["flops"] / max(d["ms"], 1e-9) / 1e9, 1)}
+                                     "tflops": round(d["flops"] / max(d["ms"], 1e-9) / 1e9, 1),
+                                     "frac_of_peak": round(d["flops"] / max(d["ms"], 1e-9) / 1e9 / pk["tflops"], 3)}
                                  for k, d in prof.items() if isinstance(d, dict)},
+                     "tensor_kernels_frac": round(sum(d["flops"] for d in prof.values() if isinstance(d, dict))
+                                                  / max(sum(d["ms"] for d in prof.values() if isinstance(d, dict)), 1e-9)
+                                                  / 1e9 / pk["tflops"], 3),
                      "attention": {"kernel": "attention_tc2_kernel (tcgen05/TMEM flash, two 128-query slots per CTA)", "launches": att["launches"],
                                    "ms": att["ms"], "achieved_tflops": att["flops"] / (att["ms"] * 1e-3) / 1e12,
                                    "share_of_eager_step": att["ms"] / prof["_step_ms_eager"]}},
